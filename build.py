@@ -1,0 +1,149 @@
+#!/usr/bin/env python3
+"""In-tree native build for the dlbb framework.
+
+Produces (next to the Python package, so the artefacts travel with a gpurun snapshot):
+
+  distributed_llm_backend_benchmark_b200/lib/libdlbb.so      CUDA kernels + collectives + bootstrap (C ABI)
+  distributed_llm_backend_benchmark_b200/lib/_dlbb_pg.so     c10d::Backend torch extension (optional)
+  bin/b200run                                                C++ launcher (mpirun / deepspeed personalities)
+
+Everything is compiled for sm_100a only (`-gencode arch=compute_100a,code=sm_100a -lineinfo`).
+nvcc cross-compiles without a GPU, so this runs on the CPU-only dev box.  Objects are cached by
+source mtime under build/.
+"""
+from __future__ import annotations
+
+import argparse
+import concurrent.futures as cf
+import os
+import shutil
+import subprocess
+import sys
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parent
+PKG = ROOT / "distributed_llm_backend_benchmark_b200"
+LIBDIR = PKG / "lib"
+BUILD = ROOT / "build"
+
+NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
+CXX = os.environ.get("CXX", "g++")
+ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
+NVCC_FLAGS = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr",
+              "-Xptxas", "-v", "-I", str(ROOT / "include")]
+CXX_FLAGS = ["-O2", "-std=c++17", "-fPIC", "-Wall", "-I", str(ROOT / "include"),
+             "-I", "/usr/local/cuda/include"]
+
+
+def _newer(src: Path, out: Path, extra: list[Path] = ()) -> bool:
+    if not out.exists():
+        return True
+    t = out.stat().st_mtime
+    deps = [src, *extra]
+    return any(d.stat().st_mtime > t for d in deps if d.exists())
+
+
+def _run(cmd: list[str], log: Path | None = None) -> None:
+    r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    if log is not None:
+        log.write_text(r.stdout)
+    if r.returncode != 0:
+        sys.stderr.write(" ".join(cmd) + "\n" + r.stdout + "\n")
+        raise RuntimeError(f"command failed: {cmd[0]} ... {cmd[-1]}")
+
+
+def _headers(*dirs: Path) -> list[Path]:
+    out: list[Path] = []
+    for d in dirs:
+        out += list(d.glob("*.cuh")) + list(d.glob("*.h")) + list(d.glob("*.hpp"))
+    return out
+
+
+def compile_cu(src: Path, watchdog: bool) -> Path:
+    obj = BUILD / (src.parent.name + "_" + src.stem + ".o")
+    hdrs = _headers(src.parent, ROOT / "include", ROOT / "csrc" / "kernels", ROOT / "csrc" / "bootstrap")
+    if _newer(src, obj, hdrs):
+        cmd = [NVCC, *ARCH, *NVCC_FLAGS, f"-DDLBB_WATCHDOG={1 if watchdog else 0}", "-c", str(src), "-o", str(obj)]
+        _run(cmd, BUILD / (obj.stem + ".ptxas.log"))
+    return obj
+
+
+def compile_cpp(src: Path, extra_flags: list[str] = ()) -> Path:
+    obj = BUILD / (src.parent.name + "_" + src.stem + ".o")
+    hdrs = _headers(src.parent, ROOT / "include", ROOT / "csrc" / "bootstrap")
+    if _newer(src, obj, hdrs):
+        _run([CXX, *CXX_FLAGS, *extra_flags, "-c", str(src), "-o", str(obj)])
+    return obj
+
+
+def build_core(watchdog: bool = True, jobs: int = 8) -> Path:
+    BUILD.mkdir(exist_ok=True)
+    LIBDIR.mkdir(exist_ok=True)
+    cu = sorted((ROOT / "csrc" / "kernels").glob("*.cu")) + sorted((ROOT / "csrc" / "collectives").glob("*.cu"))
+    cpp = sorted((ROOT / "csrc" / "bootstrap").glob("*.cpp"))
+    with cf.ThreadPoolExecutor(max_workers=jobs) as ex:
+        objs = list(ex.map(lambda s: compile_cu(s, watchdog), cu))
+        objs += list(ex.map(compile_cpp, cpp))
+    out = LIBDIR / "libdlbb.so"
+    if any(_newer(o, out) for o in objs):
+        _run([NVCC, *ARCH, "-shared", "-o", str(out), *map(str, objs), "-lcudart", "-lpthread", "-ldl"])
+    return out
+
+
+def build_launcher() -> Path | None:
+    srcs = sorted((ROOT / "csrc" / "launcher").glob("*.cpp"))
+    if not srcs:
+        return None
+    out = ROOT / "bin" / "b200run"
+    out.parent.mkdir(exist_ok=True)
+    if any(_newer(s, out, _headers(s.parent)) for s in srcs):
+        _run([CXX, "-O2", "-std=c++17", "-Wall", "-o", str(out), *map(str, srcs), "-lpthread", "-ldl"])
+    return out
+
+
+def build_pg() -> Path | None:
+    srcs = sorted((ROOT / "csrc" / "pg").glob("*.cpp"))
+    if not srcs:
+        return None
+    import sysconfig
+
+    import torch
+    from torch.utils import cpp_extension as ce
+
+    out = LIBDIR / "_dlbb_pg.so"
+    hdrs = _headers(ROOT / "csrc" / "pg", ROOT / "include")
+    if not any(_newer(s, out, hdrs) for s in srcs):
+        return out
+    inc = [f"-I{p}" for p in ce.include_paths()] + [f"-I{sysconfig.get_paths()['include']}"]
+    abi = int(torch._C._GLIBCXX_USE_CXX11_ABI)
+    flags = [*inc, f"-D_GLIBCXX_USE_CXX11_ABI={abi}", "-DTORCH_EXTENSION_NAME=_dlbb_pg",
+             "-DTORCH_API_INCLUDE_EXTENSION_H", "-DUSE_C10D_NCCL=0", "-w"]
+    objs = [compile_cpp(s, flags) for s in srcs]
+    tlib = Path(torch.__file__).parent / "lib"
+    _run([CXX, "-shared", "-o", str(out), *map(str, objs), f"-L{tlib}", f"-Wl,-rpath,{tlib}",
+          f"-L{LIBDIR}", "-Wl,-rpath,$ORIGIN", "-ldlbb", "-ltorch", "-ltorch_cpu", "-ltorch_python", "-lc10",
+          "-L/usr/local/cuda/lib64", "-lcudart"])
+    return out
+
+
+def main() -> None:
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--no-watchdog", action="store_true", help="compile device spin-wait watchdogs out")
+    ap.add_argument("--clean", action="store_true")
+    ap.add_argument("--only", choices=["core", "launcher", "pg"], default=None)
+    a = ap.parse_args()
+    if a.clean:
+        shutil.rmtree(BUILD, ignore_errors=True)
+        for f in LIBDIR.glob("*.so"):
+            f.unlink()
+    BUILD.mkdir(exist_ok=True)
+    if a.only in (None, "core"):
+        print("built", build_core(watchdog=not a.no_watchdog))
+    if a.only in (None, "launcher"):
+        print("built", build_launcher())
+    if a.only in (None, "pg"):
+        print("built", build_pg())
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,74 @@
+// Host-side helpers shared by every translation unit of libdlbb: error reporting, launch
+// accounting and small device math used by several kernels.
+#pragma once
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include <atomic>
+
+namespace dlbb {
+
+// Implemented in common.cu.
+void set_error(const char* fmt, ...);
+extern std::atomic<uint64_t> g_launch_count;
+
+inline void count_launch(int n = 1) { g_launch_count.fetch_add(n, std::memory_order_relaxed); }
+
+#define DLBB_CHECK_CUDA(expr)                                                                \
+    do {                                                                                     \
+        cudaError_t _e = (expr);                                                             \
+        if (_e != cudaSuccess) {                                                             \
+            ::dlbb::set_error("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, \
+                              __LINE__);                                                     \
+            return -1;                                                                       \
+        }                                                                                    \
+    } while (0)
+
+#define DLBB_CHECK_LAUNCH(name)                                                              \
+    do {                                                                                     \
+        cudaError_t _e = cudaGetLastError();                                                 \
+        if (_e != cudaSuccess) {                                                             \
+            ::dlbb::set_error("launch of %s failed: %s", name, cudaGetErrorString(_e));      \
+            return -1;                                                                       \
+        }                                                                                    \
+        ::dlbb::count_launch();                                                              \
+    } while (0)
+
+#define DLBB_REQUIRE(cond, ...)                                                              \
+    do {                                                                                     \
+        if (!(cond)) {                                                                       \
+            ::dlbb::set_error(__VA_ARGS__);                                                  \
+            return -2;                                                                       \
+        }                                                                                    \
+    } while (0)
+
+// ---- device math ---------------------------------------------------------------------------
+__device__ __forceinline__ float gelu_exact(float x) {
+    return 0.5f * x * (1.0f + erff(x * 0.70710678118654752f));
+}
+// d/dx gelu(x) = Phi(x) + x * phi(x)
+__device__ __forceinline__ float dgelu_exact(float x) {
+    const float cdf = 0.5f * (1.0f + erff(x * 0.70710678118654752f));
+    const float pdf = 0.39894228040143268f * __expf(-0.5f * x * x);
+    return cdf + x * pdf;
+}
+
+__device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
+    __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
+    return *reinterpret_cast<uint32_t*>(&v);
+}
+__device__ __forceinline__ float2 unpack_bf16x2(uint32_t u) {
+    __nv_bfloat162 v = *reinterpret_cast<__nv_bfloat162*>(&u);
+    return __bfloat1622float2(v);
+}
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+}  // namespace dlbb

@@ -1,0 +1,339 @@
+// LayerNorm forward / backward (bf16 activations, fp32 statistics), one CTA per row.
+// ref: models.py:122,135,222 (nn.LayerNorm(hidden, dtype=bf16)) used at models.py:156,177,236.
+//
+// The row is read once with 16-byte loads and kept in registers for both passes (mean, then
+// centred variance) so HBM traffic is exactly read-x + write-y.  Backward fuses the residual
+// branch gradient (dx = LN'(dy) + dres) and produces dgamma/dbeta through per-CTA register
+// partials that a second tiny kernel folds together (deterministic, no atomics).
+#include "../../include/dlbb.h"
+#include "common.cuh"
+
+namespace dlbb {
+
+constexpr int kLnThreads = 256;
+
+__device__ __forceinline__ float block_sum(float v, float* sh) {
+    v = warp_sum(v);
+    const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+    __syncthreads();  // protect sh from the previous use
+    if (l == 0) sh[w] = v;
+    __syncthreads();
+    float t = (l < kLnThreads / 32) ? sh[l] : 0.f;
+    return warp_sum(t);
+}
+
+// ---------------------------------------------------------------- vector path (cols % 8 == 0)
+template <int VPT>
+__global__ void __launch_bounds__(kLnThreads)
+ln_fwd_vec_kernel(const uint4* __restrict__ x, const uint4* __restrict__ gamma,
+                  const uint4* __restrict__ beta, uint4* __restrict__ y, float* __restrict__ mean_out,
+                  float* __restrict__ rstd_out, int rows, int cols, float eps) {
+    __shared__ float sh[32];
+    const int nvec = cols >> 3;
+    for (int row = blockIdx.x; row < rows; row += gridDim.x) {
+        const uint4* xr = x + (size_t)row * nvec;
+        float v[VPT][8];
+        float s = 0.f;
+#pragma unroll
+        for (int i = 0; i < VPT; ++i) {
+            const int c = threadIdx.x + i * kLnThreads;
+            if (c < nvec) {
+                const uint4 u = xr[c];
+                const float2 a = unpack_bf16x2(u.x), b = unpack_bf16x2(u.y), cc = unpack_bf16x2(u.z),
+                             d = unpack_bf16x2(u.w);
+                v[i][0] = a.x; v[i][1] = a.y; v[i][2] = b.x; v[i][3] = b.y;
+                v[i][4] = cc.x; v[i][5] = cc.y; v[i][6] = d.x; v[i][7] = d.y;
+#pragma unroll
+                for (int j = 0; j < 8; ++j) s += v[i][j];
+            } else {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) v[i][j] = 0.f;
+            }
+        }
+        const float mean = block_sum(s, sh) / cols;
+        float q = 0.f;
+#pragma unroll
+        for (int i = 0; i < VPT; ++i) {
+            const int c = threadIdx.x + i * kLnThreads;
+            if (c < nvec) {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) { const float d = v[i][j] - mean; q += d * d; }
+            }
+        }
+        const float rstd = rsqrtf(block_sum(q, sh) / cols + eps);
+        if (threadIdx.x == 0) {
+            if (mean_out) mean_out[row] = mean;
+            if (rstd_out) rstd_out[row] = rstd;
+        }
+        uint4* yr = y + (size_t)row * nvec;
+#pragma unroll
+        for (int i = 0; i < VPT; ++i) {
+            const int c = threadIdx.x + i * kLnThreads;
+            if (c < nvec) {
+                const uint4 g = gamma[c], b = beta[c];
+                const uint32_t gw[4] = {g.x, g.y, g.z, g.w}, bw[4] = {b.x, b.y, b.z, b.w};
+                uint32_t o[4];
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const float2 gg = unpack_bf16x2(gw[j]), bb = unpack_bf16x2(bw[j]);
+                    o[j] = pack_bf16x2((v[i][2 * j] - mean) * rstd * gg.x + bb.x,
+                                       (v[i][2 * j + 1] - mean) * rstd * gg.y + bb.y);
+                }
+                yr[c] = make_uint4(o[0], o[1], o[2], o[3]);
+            }
+        }
+    }
+}
+
+template <int VPT>
+__global__ void __launch_bounds__(kLnThreads)
+ln_bwd_vec_kernel(const uint4* __restrict__ dy, const uint4* __restrict__ x,
+                  const float* __restrict__ mean, const float* __restrict__ rstd,
+                  const uint4* __restrict__ gamma, const uint4* __restrict__ dres,
+                  uint4* __restrict__ dx, float* __restrict__ partials, int rows, int cols) {
+    __shared__ float sh[32];
+    const int nvec = cols >> 3;
+    float pg[VPT][8], pb[VPT][8];  // per-thread column partials of dgamma / dbeta
+    float gam[VPT][8];
+#pragma unroll
+    for (int i = 0; i < VPT; ++i) {
+        const int c = threadIdx.x + i * kLnThreads;
+        uint4 g = make_uint4(0, 0, 0, 0);
+        if (c < nvec) g = gamma[c];
+        const uint32_t gw[4] = {g.x, g.y, g.z, g.w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const float2 f = unpack_bf16x2(gw[j]);
+            gam[i][2 * j] = f.x; gam[i][2 * j + 1] = f.y;
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) { pg[i][j] = 0.f; pb[i][j] = 0.f; }
+    }
+    for (int row = blockIdx.x; row < rows; row += gridDim.x) {
+        const float mu = mean[row], rs = rstd[row];
+        const uint4* dyr = dy + (size_t)row * nvec;
+        const uint4* xr = x + (size_t)row * nvec;
+        float xh[VPT][8], g[VPT][8];
+        float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+        for (int i = 0; i < VPT; ++i) {
+            const int c = threadIdx.x + i * kLnThreads;
+            if (c < nvec) {
+                const uint4 ud = dyr[c], ux = xr[c];
+                const uint32_t dw[4] = {ud.x, ud.y, ud.z, ud.w}, xw[4] = {ux.x, ux.y, ux.z, ux.w};
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    const float2 d = unpack_bf16x2(dw[j]), xx = unpack_bf16x2(xw[j]);
+                    const float h0 = (xx.x - mu) * rs, h1 = (xx.y - mu) * rs;
+                    xh[i][2 * j] = h0; xh[i][2 * j + 1] = h1;
+                    pg[i][2 * j] += d.x * h0; pg[i][2 * j + 1] += d.y * h1;
+                    pb[i][2 * j] += d.x; pb[i][2 * j + 1] += d.y;
+                    const float g0 = d.x * gam[i][2 * j], g1 = d.y * gam[i][2 * j + 1];
+                    g[i][2 * j] = g0; g[i][2 * j + 1] = g1;
+                    s1 += g0 + g1;
+                    s2 += g0 * h0 + g1 * h1;
+                }
+            } else {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) { xh[i][j] = 0.f; g[i][j] = 0.f; }
+            }
+        }
+        const float c1 = block_sum(s1, sh) / cols;
+        const float c2 = block_sum(s2, sh) / cols;
+        uint4* dxr = dx + (size_t)row * nvec;
+#pragma unroll
+        for (int i = 0; i < VPT; ++i) {
+            const int c = threadIdx.x + i * kLnThreads;
+            if (c < nvec) {
+                float r[8];
+#pragma unroll
+                for (int j = 0; j < 8; ++j) r[j] = rs * (g[i][j] - c1 - xh[i][j] * c2);
+                if (dres) {
+                    const uint4 ur = dres[(size_t)row * nvec + c];
+                    const uint32_t rw[4] = {ur.x, ur.y, ur.z, ur.w};
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        const float2 f = unpack_bf16x2(rw[j]);
+                        r[2 * j] += f.x; r[2 * j + 1] += f.y;
+                    }
+                }
+                dxr[c] = make_uint4(pack_bf16x2(r[0], r[1]), pack_bf16x2(r[2], r[3]),
+                                    pack_bf16x2(r[4], r[5]), pack_bf16x2(r[6], r[7]));
+            }
+        }
+    }
+    // partials[blockIdx.x][0][cols] = dgamma part, [1][cols] = dbeta part
+    float* pgo = partials + (size_t)blockIdx.x * 2 * cols;
+    float* pbo = pgo + cols;
+#pragma unroll
+    for (int i = 0; i < VPT; ++i) {
+        const int c = threadIdx.x + i * kLnThreads;
+        if (c < nvec) {
+            float4* g4 = reinterpret_cast<float4*>(pgo + c * 8);
+            float4* b4 = reinterpret_cast<float4*>(pbo + c * 8);
+            g4[0] = make_float4(pg[i][0], pg[i][1], pg[i][2], pg[i][3]);
+            g4[1] = make_float4(pg[i][4], pg[i][5], pg[i][6], pg[i][7]);
+            b4[0] = make_float4(pb[i][0], pb[i][1], pb[i][2], pb[i][3]);
+            b4[1] = make_float4(pb[i][4], pb[i][5], pb[i][6], pb[i][7]);
+        }
+    }
+}
+
+// ---------------------------------------------------------------- generic path (any cols)
+__global__ void __launch_bounds__(kLnThreads)
+ln_fwd_generic_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ gamma,
+                      const __nv_bfloat16* __restrict__ beta, __nv_bfloat16* __restrict__ y,
+                      float* mean_out, float* rstd_out, int rows, int cols, float eps) {
+    __shared__ float sh[32];
+    for (int row = blockIdx.x; row < rows; row += gridDim.x) {
+        const __nv_bfloat16* xr = x + (size_t)row * cols;
+        float s = 0.f;
+        for (int c = threadIdx.x; c < cols; c += kLnThreads) s += __bfloat162float(xr[c]);
+        const float mean = block_sum(s, sh) / cols;
+        float q = 0.f;
+        for (int c = threadIdx.x; c < cols; c += kLnThreads) {
+            const float d = __bfloat162float(xr[c]) - mean;
+            q += d * d;
+        }
+        const float rstd = rsqrtf(block_sum(q, sh) / cols + eps);
+        if (threadIdx.x == 0) {
+            if (mean_out) mean_out[row] = mean;
+            if (rstd_out) rstd_out[row] = rstd;
+        }
+        for (int c = threadIdx.x; c < cols; c += kLnThreads)
+            y[(size_t)row * cols + c] =
+                __float2bfloat16((__bfloat162float(xr[c]) - mean) * rstd * __bfloat162float(gamma[c]) +
+                                 __bfloat162float(beta[c]));
+    }
+}
+
+__global__ void __launch_bounds__(kLnThreads)
+ln_bwd_generic_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
+                      const float* __restrict__ mean, const float* __restrict__ rstd,
+                      const __nv_bfloat16* __restrict__ gamma, const __nv_bfloat16* __restrict__ dres,
+                      __nv_bfloat16* __restrict__ dx, float* __restrict__ partials, int rows, int cols) {
+    __shared__ float sh[32];
+    float* pgo = partials + (size_t)blockIdx.x * 2 * cols;
+    float* pbo = pgo + cols;
+    for (int c = threadIdx.x; c < cols; c += kLnThreads) { pgo[c] = 0.f; pbo[c] = 0.f; }
+    for (int row = blockIdx.x; row < rows; row += gridDim.x) {
+        const float mu = mean[row], rs = rstd[row];
+        const size_t off = (size_t)row * cols;
+        float s1 = 0.f, s2 = 0.f;
+        for (int c = threadIdx.x; c < cols; c += kLnThreads) {
+            const float d = __bfloat162float(dy[off + c]);
+            const float h = (__bfloat162float(x[off + c]) - mu) * rs;
+            const float g = d * __bfloat162float(gamma[c]);
+            pgo[c] += d * h;  // each thread owns its columns of this CTA's slice
+            pbo[c] += d;
+            s1 += g;
+            s2 += g * h;
+        }
+        const float c1 = block_sum(s1, sh) / cols;
+        const float c2 = block_sum(s2, sh) / cols;
+        for (int c = threadIdx.x; c < cols; c += kLnThreads) {
+            const float d = __bfloat162float(dy[off + c]);
+            const float h = (__bfloat162float(x[off + c]) - mu) * rs;
+            float r = rs * (d * __bfloat162float(gamma[c]) - c1 - h * c2);
+            if (dres) r += __bfloat162float(dres[off + c]);
+            dx[off + c] = __float2bfloat16(r);
+        }
+    }
+}
+
+// Fold the per-CTA partials: one thread per column, coalesced across the CTA dimension.
+__global__ void ln_bwd_reduce_kernel(const float* __restrict__ partials, float* __restrict__ dgamma,
+                                     float* __restrict__ dbeta, int nparts, int cols) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= cols) return;
+    float g = 0.f, b = 0.f;
+    for (int p = 0; p < nparts; ++p) {
+        g += partials[(size_t)p * 2 * cols + c];
+        b += partials[(size_t)p * 2 * cols + cols + c];
+    }
+    if (dgamma) dgamma[c] = g;
+    if (dbeta) dbeta[c] = b;
+}
+
+static int ln_bwd_parts(int rows) {
+    static int sms = 0;
+    if (sms == 0) {
+        int dev = 0;
+        if (cudaGetDevice(&dev) != cudaSuccess ||
+            cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess)
+            sms = 148;
+    }
+    return rows < 2 * sms ? rows : 2 * sms;
+}
+
+}  // namespace dlbb
+
+extern "C" {
+
+int dlbb_layernorm_fwd(const void* x, const void* gamma, const void* beta, void* y, float* mean,
+                       float* rstd, int rows, int cols, float eps, void* stream) {
+    using namespace dlbb;
+    DLBB_REQUIRE(rows > 0 && cols > 0, "layernorm_fwd: empty input");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    const bool vec = (cols % 8 == 0) && cols <= 8 * kLnThreads * 4 &&
+                     ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(y) |
+                       reinterpret_cast<uintptr_t>(gamma) | reinterpret_cast<uintptr_t>(beta)) & 15) == 0;
+    const int grid = rows;
+    if (vec) {
+        const int vpt = (cols / 8 + kLnThreads - 1) / kLnThreads;
+#define LN_FWD(V)                                                                                  \
+    ln_fwd_vec_kernel<V><<<grid, kLnThreads, 0, s>>>(                                              \
+        static_cast<const uint4*>(x), static_cast<const uint4*>(gamma),                            \
+        static_cast<const uint4*>(beta), static_cast<uint4*>(y), mean, rstd, rows, cols, eps)
+        if (vpt == 1) LN_FWD(1); else if (vpt == 2) LN_FWD(2); else if (vpt == 3) LN_FWD(3); else LN_FWD(4);
+#undef LN_FWD
+    } else {
+        ln_fwd_generic_kernel<<<grid, kLnThreads, 0, s>>>(
+            static_cast<const __nv_bfloat16*>(x), static_cast<const __nv_bfloat16*>(gamma),
+            static_cast<const __nv_bfloat16*>(beta), static_cast<__nv_bfloat16*>(y), mean, rstd, rows,
+            cols, eps);
+    }
+    DLBB_CHECK_LAUNCH("layernorm_fwd");
+    return 0;
+}
+
+size_t dlbb_layernorm_bwd_scratch_bytes(int rows, int cols) {
+    return (size_t)dlbb::ln_bwd_parts(rows) * 2 * cols * sizeof(float);
+}
+
+int dlbb_layernorm_bwd(const void* dy, const void* x, const float* mean, const float* rstd,
+                       const void* gamma, const void* dres, void* dx, float* dgamma, float* dbeta,
+                       void* scratch, int rows, int cols, void* stream) {
+    using namespace dlbb;
+    DLBB_REQUIRE(rows > 0 && cols > 0, "layernorm_bwd: empty input");
+    DLBB_REQUIRE(scratch != nullptr, "layernorm_bwd: scratch is required");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    const int parts = ln_bwd_parts(rows);
+    uintptr_t al = reinterpret_cast<uintptr_t>(dy) | reinterpret_cast<uintptr_t>(x) |
+                   reinterpret_cast<uintptr_t>(gamma) | reinterpret_cast<uintptr_t>(dx) |
+                   reinterpret_cast<uintptr_t>(dres) | reinterpret_cast<uintptr_t>(scratch);
+    const bool vec = (cols % 8 == 0) && cols <= 8 * kLnThreads * 4 && (al & 15) == 0;
+    float* partials = static_cast<float*>(scratch);
+    if (vec) {
+        const int vpt = (cols / 8 + kLnThreads - 1) / kLnThreads;
+#define LN_BWD(V)                                                                                  \
+    ln_bwd_vec_kernel<V><<<parts, kLnThreads, 0, s>>>(                                             \
+        static_cast<const uint4*>(dy), static_cast<const uint4*>(x), mean, rstd,                   \
+        static_cast<const uint4*>(gamma), static_cast<const uint4*>(dres), static_cast<uint4*>(dx), \
+        partials, rows, cols)
+        if (vpt == 1) LN_BWD(1); else if (vpt == 2) LN_BWD(2); else if (vpt == 3) LN_BWD(3); else LN_BWD(4);
+#undef LN_BWD
+    } else {
+        ln_bwd_generic_kernel<<<parts, kLnThreads, 0, s>>>(
+            static_cast<const __nv_bfloat16*>(dy), static_cast<const __nv_bfloat16*>(x), mean, rstd,
+            static_cast<const __nv_bfloat16*>(gamma), static_cast<const __nv_bfloat16*>(dres),
+            static_cast<__nv_bfloat16*>(dx), partials, rows, cols);
+    }
+    DLBB_CHECK_LAUNCH("layernorm_bwd");
+    if (dgamma || dbeta) {
+        ln_bwd_reduce_kernel<<<(cols + 255) / 256, 256, 0, s>>>(partials, dgamma, dbeta, parts, cols);
+        DLBB_CHECK_LAUNCH("layernorm_bwd_reduce");
+    }
+    return 0;
+}
+}
