@@ -465,19 +465,10 @@ int dlbb_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K, i
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     int bn = g_force_bn;
     if (bn == 0) {
-        // Pick the N tile that wastes fewer SM-waves; 256 halves the smem traffic per FLOP.
-        if (g_num_sms == 0) {
-            int dev = 0;
-            DLBB_CHECK_CUDA(cudaGetDevice(&dev));
-            DLBB_CHECK_CUDA(cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev));
-        }
-        auto cost = [&](int BN, double per_tile) {
-            const long tiles = (long)((M + kBM - 1) / kBM) * ((N + BN - 1) / BN);
-            const long waves = (tiles + g_num_sms - 1) / g_num_sms;
-            return waves * per_tile;
-        };
-        // 128-wide tiles run the tensor pipe at the smem-bandwidth limit (~12% slower per FLOP).
-        bn = (N <= 128 || cost(128, 1.12) < cost(256, 2.0)) ? 128 : 256;
+        // Measured on B200 (profiles/gemm_shapes.md): the 128-wide tile is shared-memory-bandwidth
+        // bound (A and B are re-read at 128 B/clk/SM) and loses ~30% to the 256-wide tile on every
+        // model shape, even where 256 wastes part of the last wave.  Use 128 only for narrow outputs.
+        bn = (N <= 128) ? 128 : 256;
     }
     if (bn == 256)
         return dispatch_gemm<256>(A, B, C, M, N, K, lda, ldb, ldc, a_mn_major, b_mn_major, epilogue,
