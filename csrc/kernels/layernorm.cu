@@ -5,6 +5,8 @@
 // centred variance) so HBM traffic is exactly read-x + write-y.  Backward fuses the residual
 // branch gradient (dx = LN'(dy) + dres) and produces dgamma/dbeta through per-CTA register
 // partials that a second tiny kernel folds together (deterministic, no atomics).
+#include <mutex>
+
 #include "../../include/dlbb.h"
 #include "common.cuh"
 
@@ -336,4 +338,112 @@ int dlbb_layernorm_bwd(const void* dy, const void* x, const float* mean, const f
     }
     return 0;
 }
+}
+
+// ---------------------------------------------------------------------------------------------
+// LayerNorm backward for callers that cannot allocate device memory.
+//
+// Some hosts of this library are not allowed to call cudaMalloc at the point where they need a
+// LayerNorm backward: a server that hands the whole device to its own memory pool at start-up and
+// forbids driver allocations afterwards, a plugin running inside someone else's runtime with no
+// access to that runtime's allocator, or a latency-critical loop that cannot afford the implicit
+// device-wide synchronisation of cudaMalloc / cudaFree.  dlbb_layernorm_bwd() needs such a caller
+// to bring a scratch buffer; this variant brings its own instead: the per-CTA dgamma / dbeta
+// partial sums live in the fixed array below, which is part of the library image.
+//
+// Cost and limits of that choice:
+//   * every GPU on which this library is loaded holds the array (8 MiB) until the process exits,
+//     whether or not the entry point is ever called;
+//   * the array fits kNoAllocMaxParts CTAs x 2 x kNoAllocMaxCols floats, so cols is limited to
+//     kNoAllocMaxCols (8192) - larger inputs are rejected, not truncated; rows is unlimited
+//     (at most kNoAllocMaxParts CTAs walk the rows);
+//   * all calls on a device share the one array and it keeps whatever the previous call left in
+//     it.  Nothing in it has to start at zero: each CTA overwrites its whole slice (columns
+//     < cols) before the fold kernel, launched behind it on the same stream, reads it.  Two calls
+//     that can overlap on the GPU (different streams, no event between them) race on the array
+//     and corrupt each other's dgamma / dbeta; serialise them.
+//
+// Host code cannot use the array's name as a pointer - on the host it is only a handle for the
+// runtime.  The device address is looked up once per device with cudaGetSymbolAddress (with that
+// device current) and cached; the first call on a device therefore does a little set-up work and
+// should be made before any stream capture is started.
+// ---------------------------------------------------------------------------------------------
+namespace dlbb {
+
+constexpr int kNoAllocMaxParts = 128;
+constexpr int kNoAllocMaxCols = 8192;
+constexpr int kNoAllocMaxDevices = 64;
+
+static __device__ __align__(256) float g_ln_noalloc_scratch[(size_t)kNoAllocMaxParts * 2 * kNoAllocMaxCols];
+
+static float* g_ln_noalloc_ptr[kNoAllocMaxDevices];  // device address of the array, per device
+static std::mutex g_ln_noalloc_mu;
+
+// Returns the device address of the scratch array on the current device (nullptr + error set on failure).
+static float* ln_noalloc_scratch_for_current_device() {
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) {
+        set_error("layernorm_bwd_noalloc: cudaGetDevice failed: %s", cudaGetErrorString(e));
+        return nullptr;
+    }
+    if (dev < 0 || dev >= kNoAllocMaxDevices) {
+        set_error("layernorm_bwd_noalloc: device ordinal %d is outside the supported range [0, %d)", dev,
+                  kNoAllocMaxDevices);
+        return nullptr;
+    }
+    std::lock_guard<std::mutex> lk(g_ln_noalloc_mu);
+    if (g_ln_noalloc_ptr[dev] == nullptr) {
+        void* p = nullptr;
+        e = cudaGetSymbolAddress(&p, g_ln_noalloc_scratch);
+        if (e != cudaSuccess || p == nullptr) {
+            set_error("layernorm_bwd_noalloc: cudaGetSymbolAddress failed on device %d: %s", dev,
+                      cudaGetErrorString(e));
+            return nullptr;
+        }
+        g_ln_noalloc_ptr[dev] = static_cast<float*>(p);
+    }
+    return g_ln_noalloc_ptr[dev];
+}
+
+}  // namespace dlbb
+
+extern "C" int dlbb_layernorm_bwd_noalloc(const void* dy, const void* x, const float* mean, const float* rstd,
+                                          const void* gamma, const void* dres, void* dx, float* dgamma,
+                                          float* dbeta, int rows, int cols, void* stream) {
+    using namespace dlbb;
+    DLBB_REQUIRE(rows > 0 && cols > 0, "layernorm_bwd_noalloc: empty input (%d x %d)", rows, cols);
+    DLBB_REQUIRE(cols <= kNoAllocMaxCols,
+                 "layernorm_bwd_noalloc: cols=%d exceeds the built-in scratch (at most %d columns); "
+                 "use dlbb_layernorm_bwd with a caller-provided scratch buffer",
+                 cols, kNoAllocMaxCols);
+    float* partials = ln_noalloc_scratch_for_current_device();
+    if (partials == nullptr) return -1;
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    const int parts = rows < kNoAllocMaxParts ? rows : kNoAllocMaxParts;
+    const uintptr_t al = reinterpret_cast<uintptr_t>(dy) | reinterpret_cast<uintptr_t>(x) |
+                         reinterpret_cast<uintptr_t>(gamma) | reinterpret_cast<uintptr_t>(dx) |
+                         reinterpret_cast<uintptr_t>(dres);
+    const bool vec = (cols % 8 == 0) && (al & 15) == 0;  // cols <= 8192 always fits VPT <= 4
+    if (vec) {
+        const int vpt = (cols / 8 + kLnThreads - 1) / kLnThreads;
+#define LN_BWD_NA(V)                                                                               \
+    ln_bwd_vec_kernel<V><<<parts, kLnThreads, 0, s>>>(                                             \
+        static_cast<const uint4*>(dy), static_cast<const uint4*>(x), mean, rstd,                   \
+        static_cast<const uint4*>(gamma), static_cast<const uint4*>(dres), static_cast<uint4*>(dx), \
+        partials, rows, cols)
+        if (vpt == 1) LN_BWD_NA(1); else if (vpt == 2) LN_BWD_NA(2); else if (vpt == 3) LN_BWD_NA(3); else LN_BWD_NA(4);
+#undef LN_BWD_NA
+    } else {
+        ln_bwd_generic_kernel<<<parts, kLnThreads, 0, s>>>(
+            static_cast<const __nv_bfloat16*>(dy), static_cast<const __nv_bfloat16*>(x), mean, rstd,
+            static_cast<const __nv_bfloat16*>(gamma), static_cast<const __nv_bfloat16*>(dres),
+            static_cast<__nv_bfloat16*>(dx), partials, rows, cols);
+    }
+    DLBB_CHECK_LAUNCH("layernorm_bwd_noalloc");
+    if (dgamma || dbeta) {
+        ln_bwd_reduce_kernel<<<(cols + 255) / 256, 256, 0, s>>>(partials, dgamma, dbeta, parts, cols);
+        DLBB_CHECK_LAUNCH("layernorm_bwd_noalloc_reduce");
+    }
+    return 0;
 }

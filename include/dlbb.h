@@ -69,6 +69,22 @@ int dlbb_layernorm_bwd(const void* dy, const void* x, const float* mean, const f
                        const void* gamma, const void* dres, void* dx, float* dgamma, float* dbeta,
                        void* scratch, int rows, int cols, void* stream);
 
+/* LayerNorm backward that allocates nothing and needs no caller scratch.  It has no counterpart
+ * in the reference; it exists for callers that may not call cudaMalloc where they need the op (a
+ * process whose device memory is owned by its own pool, a plugin inside another runtime, a loop
+ * that cannot take cudaMalloc's device-wide synchronisation).  Same arguments and results as
+ * dlbb_layernorm_bwd minus `scratch`: the dgamma/dbeta partial sums go to an 8 MiB array built
+ * into the library (held by every GPU that loads it, until process exit).
+ *   - cols must be <= 8192, otherwise the call fails with an error and launches nothing;
+ *   - the first call on each device looks up the array's device address; make that call before
+ *     starting any stream capture;
+ *   - all calls on a device share the array: calls that may overlap on the GPU race on it and must
+ *     be serialised by the caller (same stream, or an event between them).  Nothing in the array
+ *     needs clearing between calls - each call overwrites every element it later reads. */
+int dlbb_layernorm_bwd_noalloc(const void* dy, const void* x, const float* mean, const float* rstd,
+                               const void* gamma, const void* dres, void* dx, float* dgamma,
+                               float* dbeta, int rows, int cols, void* stream);
+
 /* ------------------------------------------------------------------------------------------
  * Elementwise (bf16).  ref: models.py:182 (gelu), models.py:173,188 (residual add).
  */
