@@ -1,0 +1,59 @@
+// Internal layout of a communicator, shared by the bootstrap/VMM code (host C++) and the
+// collective launchers (CUDA).
+#pragma once
+#include <cuda.h>
+#include <stdint.h>
+
+#include <vector>
+
+#include "../../include/dlbb_comm.h"
+#include "bootstrap.h"
+
+namespace dlbb {
+
+constexpr int kMaxCtas = 128;         // channels: one signal-pad row per CTA of a collective kernel
+constexpr int kPadStride = DLBB_MAX_RANKS;  // uint32 slots per row
+// Signal pad layout (uint32 words): [kMaxCtas rows][kPadStride] for kernel barriers, then
+// a second bank of the same shape for the fused DP kernel (it runs on a side stream concurrently
+// with collectives issued on the main stream, so it must not share rows or epochs with them).
+constexpr int kPadWordsPerBank = kMaxCtas * kPadStride;
+constexpr int kPadBanks = 4;          // 0: collectives, 1: fused DP kernel, 2: fused GEMM+all-reduce, 3: point-to-point
+constexpr size_t kPadBytes = sizeof(uint32_t) * kPadWordsPerBank * kPadBanks;
+
+struct Segment {
+    bool live = false;
+    size_t size = 0;
+    CUmemGenericAllocationHandle local = 0;
+    std::vector<CUmemGenericAllocationHandle> handles;  // per rank (own = local)
+    std::vector<CUdeviceptr> va;                          // per rank mapping in this process
+    CUmemGenericAllocationHandle mc = 0;
+    CUdeviceptr mc_va = 0;
+};
+
+// What kernels receive by value.
+struct CommDev {
+    int rank, world;
+    uint32_t* pads[DLBB_MAX_RANKS];
+    char* stage[DLBB_MAX_RANKS];
+    char* stage_mc;       // multicast mapping of the staging segment (nullptr if unavailable)
+    uint32_t* pads_mc;
+};
+
+}  // namespace dlbb
+
+struct dlbb_comm {
+    int rank = 0, world = 1, device = 0;
+    dlbb::Bootstrap* bs = nullptr;
+    std::vector<dlbb::Segment> segs;
+    bool mc_supported = false;
+    size_t gran = 2u << 20;
+    int pad_seg = -1, stage_seg = -1;
+    size_t stage_bytes = 0;        // bytes of each staging region: [A][B] alternate for collectives, [C] point-to-point
+    uint32_t epoch[dlbb::kPadBanks] = {0, 0, 0, 0};  // last epoch value used on each pad bank
+    uint32_t send_epoch[DLBB_MAX_RANKS] = {};      // point-to-point: messages sent to / received from each peer
+    uint32_t recv_epoch[DLBB_MAX_RANKS] = {};
+    unsigned parity = 0;           // alternates the staging half used by single-barrier kernels
+    int ctas = 0;                  // 0 = auto
+    size_t oneshot_max = 0;        // 0 = auto
+    dlbb::CommDev dev{};
+};

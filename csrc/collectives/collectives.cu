@@ -1,0 +1,773 @@
+// Collective kernels over symmetric memory (K1-K12 of SURVEY.md section 8).
+//
+// Every collective is ONE kernel launch on the caller's stream.  Inside the kernel:
+//   1. "pack":   each rank copies its contribution from the user tensor (optionally a strided
+//                view of up to 4 dims - no .contiguous() pre-copy) into its staging region;
+//   2. barrier:  system-scope release/acquire flags on the peers' signal pads;
+//   3. "pull":   the rank reads what it needs straight out of the peers' staging regions over
+//                NVLink (plain peer loads) and reduces / scatters it into the user output.
+// Large all-reduces use the bandwidth-optimal two-shot form (reduce-scatter, then all-gather by
+// peer stores or by NVLS multimem.ld_reduce / multimem.st) with a second barrier.
+//
+// ref (what these replace): collectives/1d/dsccl.py:59-163, collectives/1d/openmpi.py:55-198,
+// collectives/3d/dsccl.py:46-118, models.py:95.
+#include <algorithm>
+
+#include "../../include/dlbb.h"
+#include "../../include/dlbb_comm.h"
+#include "coll_device.cuh"
+
+namespace dlbb {
+
+constexpr int kCollThreads = 256;
+constexpr int kU = 8;   // independent 16 B requests a thread keeps in flight (NVLink latency ~2 us)
+
+struct ViewDev {
+    int ndim;            // 0 = contiguous
+    int64_t size[4];
+    int64_t stride[4];
+};
+
+struct Piece {           // a contiguous run of elements / bytes
+    int peer;            // pull: whose staging to read (pack: unused)
+    int64_t a_off;       // pack: logical source element offset    pull: offset in the peer's staging
+    int64_t b_off;       // pack: offset in my staging              pull: offset in my output
+    int64_t n;           // elements (typed kernels) or bytes (move kernel)
+};
+
+struct PieceList {
+    int count;
+    Piece p[DLBB_MAX_RANKS];
+};
+
+__device__ __forceinline__ int64_t view_offset(const ViewDev& v, int64_t idx) {
+    if (v.ndim == 0) return idx;
+    int64_t off = 0;
+#pragma unroll
+    for (int d = 3; d >= 0; --d) {
+        if (d < v.ndim) {
+            const int64_t q = idx / v.size[d];
+            off += (idx - q * v.size[d]) * v.stride[d];
+            idx = q;
+        }
+    }
+    return off;
+}
+
+// Copy `bytes` bytes with the whole grid.  16-byte vectors when everything is aligned.
+template <bool PEER_SRC>
+__device__ __forceinline__ void grid_copy_bytes(char* dst, const char* src, int64_t bytes) {
+    const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t nth = (int64_t)gridDim.x * blockDim.x;
+    if (((reinterpret_cast<uintptr_t>(dst) | reinterpret_cast<uintptr_t>(src)) & 15) == 0) {
+        const int64_t nvec = bytes >> 4;
+        int64_t i = tid;
+        for (; i + (kU - 1) * nth < nvec; i += kU * nth) {  // kU independent 16 B requests in flight per thread
+            uint4 v[kU];
+#pragma unroll
+            for (int u = 0; u < kU; ++u)
+                v[u] = PEER_SRC ? ld_peer_v4(src + ((i + u * nth) << 4)) : ld_stream_v4(src + ((i + u * nth) << 4));
+#pragma unroll
+            for (int u = 0; u < kU; ++u) st_v4(dst + ((i + u * nth) << 4), v[u]);
+        }
+        for (; i < nvec; i += nth) st_v4(dst + (i << 4), PEER_SRC ? ld_peer_v4(src + (i << 4)) : ld_stream_v4(src + (i << 4)));
+        for (int64_t b = (nvec << 4) + tid; b < bytes; b += nth)
+            dst[b] = PEER_SRC ? ld_peer_scalar(src + b) : src[b];
+    } else {
+        for (int64_t b = tid; b < bytes; b += nth) dst[b] = PEER_SRC ? ld_peer_scalar(src + b) : src[b];
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// K1: barrier
+__global__ void barrier_kernel(CommDev c, int bank, uint32_t epoch) { row_barrier(c, bank, blockIdx.x, epoch); }
+
+// ------------------------------------------------------------------------------------------
+// K6/K7/K9/K10/K11: data movement (all-gather, broadcast, gather, scatter, all-to-all, sendrecv)
+__global__ void __launch_bounds__(kCollThreads)
+move_kernel(CommDev c, const char* __restrict__ src, char* __restrict__ dst, PieceList pack, PieceList pull,
+            ViewDev view, int elem_size, int64_t stage_off, int bank, uint32_t epoch) {
+    char* my_stage = c.stage[c.rank] + stage_off;
+    for (int i = 0; i < pack.count; ++i) {
+        const Piece& pc = pack.p[i];
+        if (view.ndim == 0) {
+            grid_copy_bytes<false>(my_stage + pc.b_off, src + pc.a_off, pc.n);
+        } else {
+            // strided source: element-wise gather (bytes of one element are contiguous)
+            const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+            const int64_t nth = (int64_t)gridDim.x * blockDim.x;
+            const int64_t nel = pc.n / elem_size, e0 = pc.a_off / elem_size;
+            for (int64_t e = tid; e < nel; e += nth) {
+                const char* s = src + view_offset(view, e0 + e) * elem_size;
+                char* d = my_stage + pc.b_off + e * elem_size;
+                if (elem_size == 2) *reinterpret_cast<uint16_t*>(d) = *reinterpret_cast<const uint16_t*>(s);
+                else if (elem_size == 4) *reinterpret_cast<uint32_t*>(d) = *reinterpret_cast<const uint32_t*>(s);
+                else if (elem_size == 8) *reinterpret_cast<uint64_t*>(d) = *reinterpret_cast<const uint64_t*>(s);
+                else for (int b = 0; b < elem_size; ++b) d[b] = s[b];
+            }
+        }
+    }
+    grid_barrier(c, bank, gridDim.x, epoch);
+    for (int i = 0; i < pull.count; ++i) {
+        const Piece& pc = pull.p[i];
+        grid_copy_bytes<true>(dst + pc.b_off, c.stage[pc.peer] + stage_off + pc.a_off, pc.n);
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// Typed pack (with optional strided view) used by the reducing kernels.
+template <typename T>
+__device__ __forceinline__ void pack_typed(T* stage, const T* __restrict__ src, const ViewDev& view, int64_t src_off,
+                                           int64_t n, int64_t tid, int64_t nth) {
+    constexpr int VE = 16 / sizeof(T);
+    if (view.ndim == 0) {
+        const T* s = src + src_off;
+        if (((reinterpret_cast<uintptr_t>(s) | reinterpret_cast<uintptr_t>(stage)) & 15) == 0) {
+            const int64_t nvec = n / VE;
+            const uint4* s4 = reinterpret_cast<const uint4*>(s);
+            uint4* d4 = reinterpret_cast<uint4*>(stage);
+            for (int64_t i0 = tid; i0 < nvec; i0 += nth * kU) {
+                uint4 b[kU];
+#pragma unroll
+                for (int u = 0; u < kU; ++u)
+                    if (i0 + u * nth < nvec) b[u] = ld_stream_v4(s4 + i0 + u * nth);
+#pragma unroll
+                for (int u = 0; u < kU; ++u)
+                    if (i0 + u * nth < nvec) st_v4(d4 + i0 + u * nth, b[u]);
+            }
+            for (int64_t i = nvec * VE + tid; i < n; i += nth) stage[i] = s[i];
+        } else {
+            for (int64_t i = tid; i < n; i += nth) stage[i] = s[i];
+        }
+        return;
+    }
+    // Strided view.  When the innermost dimension is dense and a whole number of 16 B vectors,
+    // gather vector-wise (one index decomposition per vector), else element-wise.
+    const int last = view.ndim - 1;
+    const bool vec_ok = view.stride[last] == 1 && view.size[last] % VE == 0 && src_off % VE == 0 && n % VE == 0 &&
+                        (reinterpret_cast<uintptr_t>(src) & 15) == 0 && (reinterpret_cast<uintptr_t>(stage) & 15) == 0;
+    bool strides_ok = vec_ok;
+    if (vec_ok)
+        for (int d = 0; d < last; ++d) strides_ok = strides_ok && (view.stride[d] % VE == 0);
+    if (strides_ok) {
+        const int64_t nvec = n / VE;
+        for (int64_t i = tid; i < nvec; i += nth) {
+            const int64_t off = view_offset(view, src_off + i * VE);
+            st_v4(reinterpret_cast<uint4*>(stage) + i, ld_stream_v4(src + off));
+        }
+    } else {
+        for (int64_t i = tid; i < n; i += nth) stage[i] = src[view_offset(view, src_off + i)];
+    }
+}
+
+// Reduce kU vector positions (i0 + u*stride, u < kU) across all ranks, in rank order, so every rank
+// computes bit-identical results.  All kU loads of one peer are issued before any is consumed.
+template <typename T, int OP>
+__device__ __forceinline__ void reduce_batch(const CommDev& c, int64_t base_byte_off, int64_t i0, int64_t stride,
+                                             int64_t nvec, uint4 (&out)[kU]) {
+    constexpr int VE = 16 / sizeof(T);
+    using A = typename Acc<T>::type;
+    A acc[kU][VE];
+    for (int p = 0; p < c.world; ++p) {
+        uint4 buf[kU];
+        const char* sp = c.stage[p] + base_byte_off;
+#pragma unroll
+        for (int u = 0; u < kU; ++u)
+            if (i0 + u * stride < nvec) buf[u] = ld_peer_v4(sp + ((i0 + u * stride) << 4));
+#pragma unroll
+        for (int u = 0; u < kU; ++u) {
+            if (i0 + u * stride < nvec) {
+                const T* t = reinterpret_cast<const T*>(&buf[u]);
+#pragma unroll
+                for (int e = 0; e < VE; ++e) {
+                    const A x = to_acc<T>(t[e]);
+                    acc[u][e] = (p == 0) ? x : red_op<OP, A>(acc[u][e], x);
+                }
+            }
+        }
+    }
+#pragma unroll
+    for (int u = 0; u < kU; ++u) {
+        T* ot = reinterpret_cast<T*>(&out[u]);
+#pragma unroll
+        for (int e = 0; e < VE; ++e) ot[e] = from_acc<T>(acc[u][e]);
+    }
+}
+
+template <typename T, int OP>
+__device__ __forceinline__ typename Acc<T>::type reduce_scalar(const CommDev& c, int64_t stage_byte_off) {
+    using A = typename Acc<T>::type;
+    A acc = to_acc<T>(ld_peer_scalar(reinterpret_cast<const T*>(c.stage[0] + stage_byte_off)));
+    for (int p = 1; p < c.world; ++p)
+        acc = red_op<OP, A>(acc, to_acc<T>(ld_peer_scalar(reinterpret_cast<const T*>(c.stage[p] + stage_byte_off))));
+    return acc;
+}
+
+// ------------------------------------------------------------------------------------------
+// K2/K5/K8: single-barrier reductions (one-shot all-reduce, reduce, reduce-scatter).
+// Every rank packs `pack` pieces; ranks with red_n > 0 reduce stage elements
+// [red_off, red_off + red_n) over all ranks into dst (+ extra, if given).
+template <typename T, int OP>
+__global__ void __launch_bounds__(kCollThreads)
+reduce_kernel(CommDev c, const T* __restrict__ src, T* __restrict__ dst, const T* __restrict__ extra, PieceList pack,
+              ViewDev view, int64_t red_off, int64_t red_n, int64_t stage_off, int bank, uint32_t epoch) {
+    constexpr int VE = 16 / sizeof(T);
+    using A = typename Acc<T>::type;
+    const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t nth = (int64_t)gridDim.x * blockDim.x;
+    T* my_stage = reinterpret_cast<T*>(c.stage[c.rank] + stage_off);
+    for (int i = 0; i < pack.count; ++i)
+        pack_typed<T>(my_stage + pack.p[i].b_off, src, view, pack.p[i].a_off, pack.p[i].n, tid, nth);
+    grid_barrier(c, bank, gridDim.x, epoch);
+    if (red_n <= 0) return;
+    const int64_t base_b = stage_off + red_off * (int64_t)sizeof(T);
+    const bool vec_ok = (base_b & 15) == 0 && (reinterpret_cast<uintptr_t>(dst) & 15) == 0 &&
+                        (extra == nullptr || (reinterpret_cast<uintptr_t>(extra) & 15) == 0);
+    int64_t done = 0;
+    if (vec_ok) {
+        const int64_t nvec = red_n / VE;
+        for (int64_t i0 = tid; i0 < nvec; i0 += nth * kU) {
+            uint4 o[kU];
+            reduce_batch<T, OP>(c, base_b, i0, nth, nvec, o);
+#pragma unroll
+            for (int u = 0; u < kU; ++u) {
+                const int64_t i = i0 + u * nth;
+                if (i < nvec) {
+                    if (extra) {
+                        const uint4 x = ld_stream_v4(reinterpret_cast<const uint4*>(extra) + i);
+                        const T* xt = reinterpret_cast<const T*>(&x);
+                        T* ot = reinterpret_cast<T*>(&o[u]);
+#pragma unroll
+                        for (int e = 0; e < VE; ++e) ot[e] = from_acc<T>(to_acc<T>(ot[e]) + to_acc<T>(xt[e]));
+                    }
+                    st_v4(reinterpret_cast<uint4*>(dst) + i, o[u]);
+                }
+            }
+        }
+        done = nvec * VE;
+    }
+    for (int64_t i = done + tid; i < red_n; i += nth) {
+        A a = reduce_scalar<T, OP>(c, base_b + i * (int64_t)sizeof(T));
+        if (extra) a += to_acc<T>(extra[i]);
+        dst[i] = from_acc<T>(a);
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// K3/K4: two-shot all-reduce.  CTA b owns the element range [b*per, (b+1)*per) on every rank and
+// only ever meets CTA b of the peers (row barriers), so CTAs pipeline independently:
+//   pack range -> barrier -> reduce my 1/world of the range from all ranks and store the result
+//   into every rank's out-staging -> barrier -> unpack the whole range from my out-staging.
+// NVLS variant: the reduce is multimem.ld_reduce on the in-staging multicast address and the
+// store is multimem.st on the out-staging multicast address (both performed by the switch).
+template <typename T> struct MmReduce { static constexpr bool ok = false; };
+template <> struct MmReduce<__nv_bfloat16> {
+    static constexpr bool ok = true;
+    __device__ static uint4 ld(const void* p) { return mm_ld_reduce_add_bf16(p); }
+};
+template <> struct MmReduce<__half> {
+    static constexpr bool ok = true;
+    __device__ static uint4 ld(const void* p) { return mm_ld_reduce_add_f16(p); }
+};
+template <> struct MmReduce<float> {
+    static constexpr bool ok = true;
+    __device__ static uint4 ld(const void* p) { return mm_ld_reduce_add_f32(p); }
+};
+
+template <typename T, int OP, bool NVLS>
+__global__ void __launch_bounds__(kCollThreads)
+allreduce_twoshot_kernel(CommDev c, const T* __restrict__ src, T* __restrict__ dst, const T* __restrict__ extra,
+                         ViewDev view, int64_t src_off, int64_t n, int64_t in_off, int64_t out_off, int bank,
+                         uint32_t epoch) {
+    constexpr int VE = 16 / sizeof(T);
+    using A = typename Acc<T>::type;
+    // range of this CTA, in vectors; n is a multiple of VE * world (host pads the tail separately)
+    const int64_t nvec = n / VE;
+    const int64_t per = (nvec + gridDim.x - 1) / gridDim.x;
+    const int64_t v_lo = std::min<int64_t>((int64_t)blockIdx.x * per, nvec);
+    const int64_t v_hi = std::min<int64_t>(v_lo + per, nvec);
+    const int64_t cnt = v_hi - v_lo;
+    T* my_in = reinterpret_cast<T*>(c.stage[c.rank] + in_off);
+    pack_typed<T>(my_in + v_lo * VE, src, view, src_off + v_lo * VE, cnt * VE, threadIdx.x, blockDim.x);
+    row_barrier(c, bank, blockIdx.x, epoch);
+    // my share of the CTA range
+    const int64_t share = (cnt + c.world - 1) / c.world;
+    const int64_t s_lo = std::min<int64_t>(v_lo + c.rank * share, v_hi);
+    const int64_t s_hi = std::min<int64_t>(s_lo + share, v_hi);
+    for (int64_t i0 = s_lo + threadIdx.x; i0 < s_hi; i0 += (int64_t)blockDim.x * kU) {
+        uint4 o[kU];
+        if constexpr (NVLS && MmReduce<T>::ok) {
+#pragma unroll
+            for (int u = 0; u < kU; ++u)
+                if (i0 + u * blockDim.x < s_hi) o[u] = MmReduce<T>::ld(c.stage_mc + in_off + ((i0 + u * blockDim.x) << 4));
+#pragma unroll
+            for (int u = 0; u < kU; ++u)
+                if (i0 + u * blockDim.x < s_hi) mm_st_v4(c.stage_mc + out_off + ((i0 + u * blockDim.x) << 4), o[u]);
+        } else {
+            reduce_batch<T, OP>(c, in_off, i0, blockDim.x, s_hi, o);
+#pragma unroll 1
+            for (int p = 0; p < c.world; ++p) {
+                const int q = (c.rank + p) % c.world;  // spread the store targets over the links
+                char* qp = c.stage[q] + out_off;
+#pragma unroll
+                for (int u = 0; u < kU; ++u)
+                    if (i0 + u * blockDim.x < s_hi) st_v4(qp + ((i0 + u * blockDim.x) << 4), o[u]);
+            }
+        }
+    }
+    row_barrier(c, bank, blockIdx.x, epoch + 1);
+    const uint4* my_out = reinterpret_cast<const uint4*>(c.stage[c.rank] + out_off);
+    const bool dst_vec = (reinterpret_cast<uintptr_t>(dst) & 15) == 0 &&
+                         (extra == nullptr || (reinterpret_cast<uintptr_t>(extra) & 15) == 0);
+    for (int64_t i0 = v_lo + threadIdx.x; i0 < v_hi; i0 += (int64_t)blockDim.x * kU) {
+        uint4 ob[kU];
+#pragma unroll
+        for (int u = 0; u < kU; ++u)   // written by peers during this kernel: bypass L1
+            if (i0 + u * blockDim.x < v_hi) ob[u] = ld_peer_v4(my_out + i0 + u * blockDim.x);
+#pragma unroll
+        for (int u = 0; u < kU; ++u) {
+            const int64_t i = i0 + u * blockDim.x;
+            if (i >= v_hi) continue;
+            uint4 o = ob[u];
+            if (extra) {
+                T* ot = reinterpret_cast<T*>(&o);
+                if (dst_vec) {
+                    const uint4 x = ld_stream_v4(reinterpret_cast<const uint4*>(extra) + i);
+                    const T* xt = reinterpret_cast<const T*>(&x);
+#pragma unroll
+                    for (int e = 0; e < VE; ++e) ot[e] = from_acc<T>(to_acc<T>(ot[e]) + to_acc<T>(xt[e]));
+                } else {
+#pragma unroll
+                    for (int e = 0; e < VE; ++e) ot[e] = from_acc<T>(to_acc<T>(ot[e]) + to_acc<T>(extra[i * VE + e]));
+                }
+            }
+            if (dst_vec) {
+                st_v4(reinterpret_cast<uint4*>(dst) + i, o);
+            } else {
+                const T* ot = reinterpret_cast<const T*>(&o);
+#pragma unroll
+                for (int e = 0; e < VE; ++e) dst[i * VE + e] = ot[e];
+            }
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// K11: point-to-point.  Only the two ranks of a message take part, so it has its own staging region
+// (one slot per destination inside the sender's region), its own pad bank and per-pair epochs:
+//   sender:   wait until the receiver has consumed the previous message of this pair (ack flag),
+//             pack into the slot, raise the data flag on the receiver's pad;
+//   receiver: wait for the data flag, pull from the sender's slot, raise the ack flag.
+// Each CTA handles a fixed 1/kP2PCtas of the chunk with its own pair of flags, so the CTAs of one
+// kernel never wait for each other.  A ring sendrecv runs both roles in one kernel.
+constexpr int kP2PCtas = 16;
+constexpr int kP2PBank = 3;
+
+__global__ void __launch_bounds__(kCollThreads)
+p2p_kernel(CommDev c, const char* __restrict__ send_src, int64_t send_bytes, int send_peer, uint32_t send_epoch,
+           char* __restrict__ recv_dst, int64_t recv_bytes, int recv_peer, uint32_t recv_epoch, int64_t region_off,
+           int64_t slot_bytes) {
+    const int b = blockIdx.x;
+    auto range = [&](int64_t bytes, int64_t& lo, int64_t& hi) {
+        const int64_t per = ((bytes + gridDim.x - 1) / gridDim.x + 255) / 256 * 256;
+        lo = std::min<int64_t>((int64_t)b * per, bytes);
+        hi = std::min<int64_t>(lo + per, bytes);
+    };
+    auto cta_copy = [&](char* dst, const char* src, int64_t n, bool peer) {
+        if (((reinterpret_cast<uintptr_t>(dst) | reinterpret_cast<uintptr_t>(src)) & 15) == 0) {
+            const int64_t nvec = n >> 4;
+            for (int64_t i = threadIdx.x; i < nvec; i += blockDim.x)
+                st_v4(dst + (i << 4), peer ? ld_peer_v4(src + (i << 4)) : ld_stream_v4(src + (i << 4)));
+            for (int64_t i = (nvec << 4) + threadIdx.x; i < n; i += blockDim.x)
+                dst[i] = peer ? ld_peer_scalar(src + i) : src[i];
+        } else {
+            for (int64_t i = threadIdx.x; i < n; i += blockDim.x) dst[i] = peer ? ld_peer_scalar(src + i) : src[i];
+        }
+    };
+    if (send_peer >= 0) {
+        int64_t lo, hi;
+        range(send_bytes, lo, hi);
+        if (threadIdx.x == 0) wait_flag(pad_slot(c, c.rank, kP2PBank, kP2PCtas + b, send_peer), send_epoch - 1, send_peer);
+        __syncthreads();
+        cta_copy(c.stage[c.rank] + region_off + send_peer * slot_bytes + lo, send_src + lo, hi - lo, false);
+        __syncthreads();
+        if (threadIdx.x == 0) st_release_sys(pad_slot(c, send_peer, kP2PBank, b, c.rank), send_epoch);
+    }
+    if (recv_peer >= 0) {
+        int64_t lo, hi;
+        range(recv_bytes, lo, hi);
+        if (threadIdx.x == 0) wait_flag(pad_slot(c, c.rank, kP2PBank, b, recv_peer), recv_epoch, recv_peer);
+        __syncthreads();
+        cta_copy(recv_dst + lo, c.stage[recv_peer] + region_off + c.rank * slot_bytes + lo, hi - lo, true);
+        __syncthreads();
+        if (threadIdx.x == 0) st_release_sys(pad_slot(c, recv_peer, kP2PBank, kP2PCtas + b, c.rank), recv_epoch);
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// host side
+static int pick_ctas(const dlbb_comm* c, int64_t bytes) {
+    int n = c->ctas;
+    if (n <= 0) {
+        // one CTA per 128 KiB, capped: enough loads in flight to cover ~2 us of NVLink latency
+        n = static_cast<int>(std::min<int64_t>(96, std::max<int64_t>(1, bytes / (64 << 10))));
+    }
+    return std::min(n, kMaxCtas);
+}
+
+static int64_t next_stage_off(dlbb_comm* c) {
+    const int64_t off = (c->parity & 1) ? static_cast<int64_t>(c->stage_bytes) : 0;
+    c->parity ^= 1;
+    return off;
+}
+
+static ViewDev make_view(const dlbb_view_t* v) {
+    ViewDev d{};
+    if (v && v->ndim > 0) {
+        d.ndim = v->ndim;
+        for (int i = 0; i < 4; ++i) { d.size[i] = v->size[i]; d.stride[i] = v->stride[i]; }
+    }
+    return d;
+}
+
+static size_t dtype_size(int dt) {
+    switch (dt) {
+        case DLBB_F16: case DLBB_BF16: return 2;
+        case DLBB_F32: return 4;
+        case DLBB_F64: return 8;
+        case DLBB_U8: return 1;
+    }
+    return 0;
+}
+
+template <typename T, int OP>
+static int launch_reduce_T(dlbb_comm* c, const void* src, void* dst, const void* extra, const PieceList& pack,
+                           const ViewDev& view, int64_t red_off, int64_t red_n, int64_t bytes_hint, cudaStream_t s) {
+    const int ctas = pick_ctas(c, bytes_hint);
+    const int64_t so = next_stage_off(c);
+    const uint32_t ep = ++c->epoch[0];
+    reduce_kernel<T, OP><<<ctas, kCollThreads, 0, s>>>(c->dev, static_cast<const T*>(src), static_cast<T*>(dst),
+                                                       static_cast<const T*>(extra), pack, view, red_off, red_n, so, 0,
+                                                       ep);
+    DLBB_CHECK_LAUNCH("reduce_kernel");
+    return 0;
+}
+
+template <typename T>
+static int launch_reduce_op(dlbb_comm* c, int op, const void* src, void* dst, const void* extra, const PieceList& pack,
+                            const ViewDev& view, int64_t red_off, int64_t red_n, int64_t bytes_hint, cudaStream_t s) {
+    switch (op) {
+        case DLBB_SUM: return launch_reduce_T<T, DLBB_SUM>(c, src, dst, extra, pack, view, red_off, red_n, bytes_hint, s);
+        case DLBB_MAX: return launch_reduce_T<T, DLBB_MAX>(c, src, dst, extra, pack, view, red_off, red_n, bytes_hint, s);
+        case DLBB_MIN: return launch_reduce_T<T, DLBB_MIN>(c, src, dst, extra, pack, view, red_off, red_n, bytes_hint, s);
+        case DLBB_PROD: return launch_reduce_T<T, DLBB_PROD>(c, src, dst, extra, pack, view, red_off, red_n, bytes_hint, s);
+    }
+    set_error("unknown reduce op %d", op);
+    return -2;
+}
+
+static int launch_reduce(dlbb_comm* c, int dtype, int op, const void* src, void* dst, const void* extra,
+                         const PieceList& pack, const ViewDev& view, int64_t red_off, int64_t red_n,
+                         int64_t bytes_hint, cudaStream_t s) {
+    switch (dtype) {
+        case DLBB_F16: return launch_reduce_op<__half>(c, op, src, dst, extra, pack, view, red_off, red_n, bytes_hint, s);
+        case DLBB_BF16: return launch_reduce_op<__nv_bfloat16>(c, op, src, dst, extra, pack, view, red_off, red_n, bytes_hint, s);
+        case DLBB_F32: return launch_reduce_op<float>(c, op, src, dst, extra, pack, view, red_off, red_n, bytes_hint, s);
+        case DLBB_F64: return launch_reduce_op<double>(c, op, src, dst, extra, pack, view, red_off, red_n, bytes_hint, s);
+    }
+    set_error("reduction on unsupported dtype %d", dtype);
+    return -2;
+}
+
+template <typename T, int OP>
+static int launch_twoshot_T(dlbb_comm* c, bool nvls, const void* src, void* dst, const void* extra, const ViewDev& view,
+                            int64_t src_off, int64_t n, cudaStream_t s) {
+    const int ctas = c->ctas > 0 ? std::min(c->ctas, kMaxCtas) : static_cast<int>(std::min<int64_t>(
+        96, std::max<int64_t>(1, n * (int64_t)sizeof(T) / (128 << 10))));
+    const int64_t in_off = next_stage_off(c);
+    const int64_t out_off = in_off == 0 ? static_cast<int64_t>(c->stage_bytes) : 0;
+    const uint32_t ep = c->epoch[0] + 1;
+    c->epoch[0] += 2;
+    if (nvls && MmReduce<T>::ok && OP == DLBB_SUM)
+        allreduce_twoshot_kernel<T, OP, true><<<ctas, kCollThreads, 0, s>>>(
+            c->dev, static_cast<const T*>(src), static_cast<T*>(dst), static_cast<const T*>(extra), view, src_off, n,
+            in_off, out_off, 0, ep);
+    else
+        allreduce_twoshot_kernel<T, OP, false><<<ctas, kCollThreads, 0, s>>>(
+            c->dev, static_cast<const T*>(src), static_cast<T*>(dst), static_cast<const T*>(extra), view, src_off, n,
+            in_off, out_off, 0, ep);
+    DLBB_CHECK_LAUNCH("allreduce_twoshot_kernel");
+    return 0;
+}
+
+template <typename T>
+static int launch_twoshot_op(dlbb_comm* c, int op, bool nvls, const void* src, void* dst, const void* extra,
+                             const ViewDev& view, int64_t src_off, int64_t n, cudaStream_t s) {
+    switch (op) {
+        case DLBB_SUM: return launch_twoshot_T<T, DLBB_SUM>(c, nvls, src, dst, extra, view, src_off, n, s);
+        case DLBB_MAX: return launch_twoshot_T<T, DLBB_MAX>(c, false, src, dst, extra, view, src_off, n, s);
+        case DLBB_MIN: return launch_twoshot_T<T, DLBB_MIN>(c, false, src, dst, extra, view, src_off, n, s);
+        case DLBB_PROD: return launch_twoshot_T<T, DLBB_PROD>(c, false, src, dst, extra, view, src_off, n, s);
+    }
+    set_error("unknown reduce op %d", op);
+    return -2;
+}
+
+static int launch_twoshot(dlbb_comm* c, int dtype, int op, bool nvls, const void* src, void* dst, const void* extra,
+                          const ViewDev& view, int64_t src_off, int64_t n, cudaStream_t s) {
+    switch (dtype) {
+        case DLBB_F16: return launch_twoshot_op<__half>(c, op, nvls, src, dst, extra, view, src_off, n, s);
+        case DLBB_BF16: return launch_twoshot_op<__nv_bfloat16>(c, op, nvls, src, dst, extra, view, src_off, n, s);
+        case DLBB_F32: return launch_twoshot_op<float>(c, op, nvls, src, dst, extra, view, src_off, n, s);
+        case DLBB_F64: return launch_twoshot_op<double>(c, op, false, src, dst, extra, view, src_off, n, s);
+    }
+    set_error("reduction on unsupported dtype %d", dtype);
+    return -2;
+}
+
+static int launch_move(dlbb_comm* c, const void* src, void* dst, const PieceList& pack, const PieceList& pull,
+                       const ViewDev& view, int elem_size, int64_t bytes_hint, cudaStream_t s) {
+    const int ctas = pick_ctas(c, bytes_hint);
+    const int64_t so = next_stage_off(c);
+    const uint32_t ep = ++c->epoch[0];
+    move_kernel<<<ctas, kCollThreads, 0, s>>>(c->dev, static_cast<const char*>(src), static_cast<char*>(dst), pack, pull,
+                                              view, elem_size, so, 0, ep);
+    DLBB_CHECK_LAUNCH("move_kernel");
+    return 0;
+}
+
+static int allreduce_impl(dlbb_comm* c, const void* in, void* out, const void* extra, int64_t count, int dtype, int op,
+                          int algo, const dlbb_view_t* in_view, cudaStream_t s) {
+    const size_t es = dtype_size(dtype);
+    DLBB_REQUIRE(es != 0 && dtype != DLBB_U8, "allreduce: unsupported dtype %d", dtype);
+    DLBB_REQUIRE(count >= 0, "allreduce: negative count");
+    if (count == 0) return 0;
+    const ViewDev view = make_view(in_view);
+    const int64_t VE = 16 / (int64_t)es;
+    const int64_t cap = static_cast<int64_t>(c->stage_bytes / es) / (VE * c->world) * (VE * c->world);
+    const int64_t oneshot_max = c->oneshot_max ? (int64_t)c->oneshot_max : (c->world <= 2 ? (4 << 20) : (512 << 10));
+    const bool nvls_ok = dlbb_comm_has_multicast(c) && op == DLBB_SUM && dtype != DLBB_F64;
+    int64_t done = 0;
+    while (done < count) {
+        const int64_t left = count - done;
+        const int64_t bytes = left * (int64_t)es;
+        bool oneshot = algo == DLBB_ALGO_ONESHOT || (algo == DLBB_ALGO_AUTO && bytes <= oneshot_max) || c->world == 1;
+        // two-shot works on multiples of VE*world elements; a ragged tail goes through one-shot
+        int64_t n = std::min(left, cap);
+        if (!oneshot) {
+            n = n / (VE * c->world) * (VE * c->world);
+            if (n == 0) { oneshot = true; n = std::min(left, cap); }
+        }
+        const char* ext = extra ? static_cast<const char*>(extra) + done * es : nullptr;
+        char* o = static_cast<char*>(out) + done * es;
+        int rc;
+        if (oneshot) {
+            PieceList pack{};
+            pack.count = 1;
+            pack.p[0] = Piece{0, done, 0, n};
+            rc = launch_reduce(c, dtype, op, in, o, ext, pack, view, 0, n, n * es, s);
+        } else {
+            const bool nvls = nvls_ok && (algo == DLBB_ALGO_NVLS || algo == DLBB_ALGO_AUTO);
+            rc = launch_twoshot(c, dtype, op, nvls, in, o, ext, view, done, n, s);
+        }
+        if (rc) return rc;
+        done += n;
+    }
+    return 0;
+}
+
+}  // namespace dlbb
+
+using namespace dlbb;
+
+extern "C" {
+
+int dlbb_barrier(dlbb_comm_t* c, void* stream) {
+    const uint32_t ep = ++c->epoch[0];
+    barrier_kernel<<<1, 32, 0, static_cast<cudaStream_t>(stream)>>>(c->dev, 0, ep);
+    DLBB_CHECK_LAUNCH("barrier_kernel");
+    return 0;
+}
+
+int dlbb_allreduce(dlbb_comm_t* c, const void* in, void* out, int64_t count, int dtype, int op, int algo,
+                   const dlbb_view_t* in_view, void* stream) {
+    return allreduce_impl(c, in, out, nullptr, count, dtype, op, algo, in_view, static_cast<cudaStream_t>(stream));
+}
+
+int dlbb_allreduce_residual_bf16(dlbb_comm_t* c, const void* in, const void* residual, void* out, int64_t count,
+                                 void* stream) {
+    return allreduce_impl(c, in, out, residual, count, DLBB_BF16, DLBB_SUM, DLBB_ALGO_AUTO, nullptr,
+                          static_cast<cudaStream_t>(stream));
+}
+
+int dlbb_reduce(dlbb_comm_t* c, const void* in, void* out, int64_t count, int dtype, int op, int root, void* stream) {
+    const size_t es = dtype_size(dtype);
+    DLBB_REQUIRE(es != 0 && dtype != DLBB_U8, "reduce: unsupported dtype %d", dtype);
+    DLBB_REQUIRE(root >= 0 && root < c->world, "reduce: bad root %d", root);
+    const int64_t cap = static_cast<int64_t>(c->stage_bytes / es);
+    for (int64_t done = 0; done < count; done += cap) {
+        const int64_t n = std::min(cap, count - done);
+        PieceList pack{};
+        pack.count = 1;
+        pack.p[0] = Piece{0, done, 0, n};
+        const int rc = launch_reduce(c, dtype, op, in, static_cast<char*>(out) + done * es, nullptr, pack, ViewDev{}, 0,
+                                     c->rank == root ? n : 0, n * es, static_cast<cudaStream_t>(stream));
+        if (rc) return rc;
+    }
+    return 0;
+}
+
+int dlbb_reduce_scatter(dlbb_comm_t* c, const void* in, void* out, int64_t cpr, int dtype, int op, void* stream) {
+    const size_t es = dtype_size(dtype);
+    DLBB_REQUIRE(es != 0 && dtype != DLBB_U8, "reduce_scatter: unsupported dtype %d", dtype);
+    // per launch every rank stages `chunk` elements for each destination rank
+    int64_t cap = static_cast<int64_t>(c->stage_bytes / es) / c->world;
+    cap = cap / 16 * 16;
+    DLBB_REQUIRE(cap > 0, "reduce_scatter: staging too small");
+    for (int64_t done = 0; done < cpr; done += cap) {
+        const int64_t n = std::min(cap, cpr - done);
+        const int64_t slot = (n + 15) / 16 * 16;  // keep every destination slot 16 B aligned
+        PieceList pack{};
+        pack.count = c->world;
+        for (int p = 0; p < c->world; ++p) pack.p[p] = Piece{0, p * cpr + done, p * slot, n};
+        const int rc = launch_reduce(c, dtype, op, in, static_cast<char*>(out) + done * es, nullptr, pack, ViewDev{},
+                                     c->rank * slot, n, n * es * c->world, static_cast<cudaStream_t>(stream));
+        if (rc) return rc;
+    }
+    return 0;
+}
+
+int dlbb_allgather(dlbb_comm_t* c, const void* in, void* out, int64_t cpr, int dtype, const dlbb_view_t* in_view,
+                   void* stream) {
+    const int64_t es = (int64_t)dtype_size(dtype);
+    DLBB_REQUIRE(es != 0, "allgather: unsupported dtype %d", dtype);
+    const int64_t total = cpr * es;
+    const int64_t cap = static_cast<int64_t>(c->stage_bytes) / 64 * 64;
+    const ViewDev view = make_view(in_view);
+    for (int64_t done = 0; done < total; done += cap) {
+        const int64_t n = std::min(cap, total - done);
+        PieceList pack{}, pull{};
+        pack.count = 1;
+        pack.p[0] = Piece{0, done, 0, n};
+        pull.count = c->world;
+        for (int i = 0; i < c->world; ++i) {
+            const int p = (c->rank + i) % c->world;  // start with my own copy, spread peers over time
+            pull.p[i] = Piece{p, 0, p * total + done, n};
+        }
+        const int rc = launch_move(c, in, out, pack, pull, view, (int)es, n * c->world, static_cast<cudaStream_t>(stream));
+        if (rc) return rc;
+    }
+    return 0;
+}
+
+int dlbb_broadcast(dlbb_comm_t* c, void* buf, int64_t count, int dtype, int root, void* stream) {
+    const int64_t es = (int64_t)dtype_size(dtype);
+    DLBB_REQUIRE(es != 0, "broadcast: unsupported dtype %d", dtype);
+    DLBB_REQUIRE(root >= 0 && root < c->world, "broadcast: bad root %d", root);
+    const int64_t total = count * es, cap = static_cast<int64_t>(c->stage_bytes) / 64 * 64;
+    for (int64_t done = 0; done < total; done += cap) {
+        const int64_t n = std::min(cap, total - done);
+        PieceList pack{}, pull{};
+        if (c->rank == root) { pack.count = 1; pack.p[0] = Piece{0, done, 0, n}; }
+        else { pull.count = 1; pull.p[0] = Piece{root, 0, done, n}; }
+        const int rc = launch_move(c, buf, buf, pack, pull, ViewDev{}, (int)es, n, static_cast<cudaStream_t>(stream));
+        if (rc) return rc;
+    }
+    return 0;
+}
+
+int dlbb_gather(dlbb_comm_t* c, const void* in, void* out, int64_t count, int dtype, int root, void* stream) {
+    const int64_t es = (int64_t)dtype_size(dtype);
+    DLBB_REQUIRE(es != 0, "gather: unsupported dtype %d", dtype);
+    DLBB_REQUIRE(root >= 0 && root < c->world, "gather: bad root %d", root);
+    const int64_t total = count * es, cap = static_cast<int64_t>(c->stage_bytes) / 64 * 64;
+    for (int64_t done = 0; done < total; done += cap) {
+        const int64_t n = std::min(cap, total - done);
+        PieceList pack{}, pull{};
+        pack.count = 1;
+        pack.p[0] = Piece{0, done, 0, n};
+        if (c->rank == root) {
+            pull.count = c->world;
+            for (int p = 0; p < c->world; ++p) pull.p[p] = Piece{p, 0, p * total + done, n};
+        }
+        const int rc = launch_move(c, in, out, pack, pull, ViewDev{}, (int)es, n * c->world, static_cast<cudaStream_t>(stream));
+        if (rc) return rc;
+    }
+    return 0;
+}
+
+int dlbb_scatter(dlbb_comm_t* c, const void* in, void* out, int64_t count, int dtype, int root, void* stream) {
+    const int64_t es = (int64_t)dtype_size(dtype);
+    DLBB_REQUIRE(es != 0, "scatter: unsupported dtype %d", dtype);
+    DLBB_REQUIRE(root >= 0 && root < c->world, "scatter: bad root %d", root);
+    const int64_t total = count * es;
+    const int64_t cap = static_cast<int64_t>(c->stage_bytes) / c->world / 64 * 64;
+    DLBB_REQUIRE(cap > 0, "scatter: staging too small");
+    for (int64_t done = 0; done < total; done += cap) {
+        const int64_t n = std::min(cap, total - done);
+        const int64_t slot = (n + 63) / 64 * 64;
+        PieceList pack{}, pull{};
+        if (c->rank == root) {
+            pack.count = c->world;
+            for (int p = 0; p < c->world; ++p) pack.p[p] = Piece{0, p * total + done, p * slot, n};
+        }
+        pull.count = 1;
+        pull.p[0] = Piece{root, c->rank * slot, done, n};
+        const int rc = launch_move(c, in, out, pack, pull, ViewDev{}, (int)es, n * c->world, static_cast<cudaStream_t>(stream));
+        if (rc) return rc;
+    }
+    return 0;
+}
+
+int dlbb_alltoall(dlbb_comm_t* c, const void* in, void* out, int64_t cpr, int dtype, void* stream) {
+    const int64_t es = (int64_t)dtype_size(dtype);
+    DLBB_REQUIRE(es != 0, "alltoall: unsupported dtype %d", dtype);
+    const int64_t total = cpr * es;
+    const int64_t cap = static_cast<int64_t>(c->stage_bytes) / c->world / 64 * 64;
+    DLBB_REQUIRE(cap > 0, "alltoall: staging too small");
+    for (int64_t done = 0; done < total; done += cap) {
+        const int64_t n = std::min(cap, total - done);
+        const int64_t slot = (n + 63) / 64 * 64;
+        PieceList pack{}, pull{};
+        pack.count = c->world;
+        for (int p = 0; p < c->world; ++p) pack.p[p] = Piece{0, p * total + done, p * slot, n};
+        pull.count = c->world;
+        for (int i = 0; i < c->world; ++i) {
+            const int p = (c->rank + i) % c->world;
+            pull.p[i] = Piece{p, c->rank * slot, p * total + done, n};
+        }
+        const int rc = launch_move(c, in, out, pack, pull, ViewDev{}, (int)es, n * c->world, static_cast<cudaStream_t>(stream));
+        if (rc) return rc;
+    }
+    return 0;
+}
+
+int dlbb_sendrecv(dlbb_comm_t* c, const void* send_buf, int64_t send_count, int send_peer, void* recv_buf,
+                  int64_t recv_count, int recv_peer, int dtype, void* stream) {
+    const int64_t es = (int64_t)dtype_size(dtype);
+    DLBB_REQUIRE(es != 0, "sendrecv: unsupported dtype %d", dtype);
+    DLBB_REQUIRE(send_peer < c->world && recv_peer < c->world, "sendrecv: bad peer");
+    DLBB_REQUIRE(send_peer != c->rank && recv_peer != c->rank, "sendrecv: a rank cannot message itself");
+    const int64_t sb = send_peer >= 0 ? send_count * es : 0, rb = recv_peer >= 0 ? recv_count * es : 0;
+    const int64_t slot = static_cast<int64_t>(c->stage_bytes) / c->world / 256 * 256;
+    DLBB_REQUIRE(slot > 0, "sendrecv: staging too small");
+    const int64_t region = 2 * static_cast<int64_t>(c->stage_bytes);
+    // Message k of a directed pair uses epoch k on that pair's flags; long messages are cut into
+    // slot-sized chunks, each its own epoch, sender and receiver advancing in lock step.
+    const int64_t ns = send_peer >= 0 ? std::max<int64_t>(1, (sb + slot - 1) / slot) : 0;
+    const int64_t nr = recv_peer >= 0 ? std::max<int64_t>(1, (rb + slot - 1) / slot) : 0;
+    for (int64_t k = 0; k < std::max(ns, nr); ++k) {
+        const bool do_s = k < ns, do_r = k < nr;
+        const int64_t sn = do_s ? std::max<int64_t>(0, std::min(slot, sb - k * slot)) : 0;
+        const int64_t rn = do_r ? std::max<int64_t>(0, std::min(slot, rb - k * slot)) : 0;
+        const uint32_t se = do_s ? ++c->send_epoch[send_peer] : 0;
+        const uint32_t re = do_r ? ++c->recv_epoch[recv_peer] : 0;
+        p2p_kernel<<<kP2PCtas, kCollThreads, 0, static_cast<cudaStream_t>(stream)>>>(
+            c->dev, static_cast<const char*>(send_buf) + k * slot, sn, do_s ? send_peer : -1, se,
+            static_cast<char*>(recv_buf) + k * slot, rn, do_r ? recv_peer : -1, re, region, slot);
+        DLBB_CHECK_LAUNCH("p2p_kernel");
+    }
+    return 0;
+}
+
+}  // extern "C"

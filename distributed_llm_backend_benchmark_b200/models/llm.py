@@ -104,7 +104,8 @@ class LLMEngine:
 
     def __init__(self, cfg: LLMConfig, device: torch.device | str = "cpu", tp_rank: int = 0, tp_size: int = 1,
                  seed: int | None = None, allreduce: Callable | None = None, training: bool = False,
-                 eps: float = 1e-5):
+                 eps: float = 1e-5, param_buffer: torch.Tensor | None = None,
+                 grad_buffer: torch.Tensor | None = None):
         self.cfg = cfg
         self.device = torch.device(device)
         self.tp_rank, self.tp_size = tp_rank, tp_size
@@ -116,7 +117,13 @@ class LLMEngine:
         self.layer_numel = cfg.params_per_layer(tp_size)
         self.total_numel = L * self.layer_numel + 2 * H
         # Flat parameter buffer: L layer buckets then the final LayerNorm.
-        self.params = torch.empty(self.total_numel, dtype=torch.bfloat16, device=self.device)
+        # (The data-parallel engine passes buffers that live in symmetric memory so peers can
+        # read gradients and write parameters directly.)
+        if param_buffer is not None:
+            assert param_buffer.dtype == torch.bfloat16 and param_buffer.numel() >= self.total_numel
+            self.params = param_buffer[:self.total_numel]
+        else:
+            self.params = torch.empty(self.total_numel, dtype=torch.bfloat16, device=self.device)
         self.layers = [_LayerView(self.params[i * self.layer_numel:(i + 1) * self.layer_numel], H, F, tp_size)
                        for i in range(L)]
         self.lnf_g = self.params[L * self.layer_numel:L * self.layer_numel + H]
@@ -130,7 +137,12 @@ class LLMEngine:
             if tp_size != 1:
                 raise NotImplementedError("training runs data-parallel (tp_size must be 1); the tensor-parallel "
                                           "path is the forward benchmark of run_mpi.py")
-            self.grads = torch.zeros(self.total_numel, dtype=torch.bfloat16, device=self.device)
+            if grad_buffer is not None:
+                assert grad_buffer.dtype == torch.bfloat16 and grad_buffer.numel() >= self.total_numel
+                self.grads = grad_buffer[:self.total_numel]
+                self.grads.zero_()
+            else:
+                self.grads = torch.zeros(self.total_numel, dtype=torch.bfloat16, device=self.device)
             self.glayers = [_LayerView(self.grads[i * self.layer_numel:(i + 1) * self.layer_numel], H, F, 1)
                             for i in range(L)]
             self.glnf_g = self.grads[L * self.layer_numel:L * self.layer_numel + H]

@@ -34,12 +34,14 @@ class Trainer:
                                                   pin_memory=self.device.type == "cuda")
         self.batch_size = config["input"]["batch_size"]
         if backend == "native":
-            self.engine = LLMEngine(self.model_cfg, self.device, seed=seed, training=True)
-            comm = None
+            comm, pbuf, gbuf = None, None, None
             if self.world > 1:
                 from .parallel.symm import SymmComm
-                comm = SymmComm.from_torch_distributed(self.device)
+                comm = SymmComm.from_env(self.device)
+                pbuf, gbuf = comm.alloc_dp_buffers(self.model_cfg.num_parameters(1))
             self.comm = comm
+            self.engine = LLMEngine(self.model_cfg, self.device, seed=seed, training=True, param_buffer=pbuf,
+                                    grad_buffer=gbuf)
             self.dp = DataParallelTrainer(self.engine, lr=lr, comm=comm, overlap=overlap)
             self._step = self.dp.step
         elif backend == "torch-nccl":
