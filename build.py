@@ -121,8 +121,8 @@ def build_pg() -> Path | None:
     objs = [compile_cpp(s, flags) for s in srcs]
     tlib = Path(torch.__file__).parent / "lib"
     _run([CXX, "-shared", "-o", str(out), *map(str, objs), f"-L{tlib}", f"-Wl,-rpath,{tlib}",
-          f"-L{LIBDIR}", "-Wl,-rpath,$ORIGIN", "-ldlbb", "-ltorch", "-ltorch_cpu", "-ltorch_python", "-lc10",
-          "-L/usr/local/cuda/lib64", "-lcudart"])
+          f"-L{LIBDIR}", "-Wl,-rpath,$ORIGIN", "-ldlbb", "-ltorch", "-ltorch_cpu", "-ltorch_cuda", "-ltorch_python",
+          "-lc10", "-lc10_cuda", "-L/usr/local/cuda/lib64", "-lcudart"])
     return out
 
 

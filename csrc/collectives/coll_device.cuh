@@ -138,17 +138,23 @@ __device__ __forceinline__ void mm_st_v4(void* mc, const uint4& v) {
 // ------------------------------------------------------------------ typed reduction
 template <typename T> struct Acc { using type = float; };
 template <> struct Acc<double> { using type = double; };
+template <> struct Acc<int32_t> { using type = int32_t; };
+template <> struct Acc<int64_t> { using type = int64_t; };
 
 template <typename T> __device__ __forceinline__ typename Acc<T>::type to_acc(T v);
 template <> __device__ __forceinline__ float to_acc<__half>(__half v) { return __half2float(v); }
 template <> __device__ __forceinline__ float to_acc<__nv_bfloat16>(__nv_bfloat16 v) { return __bfloat162float(v); }
 template <> __device__ __forceinline__ float to_acc<float>(float v) { return v; }
 template <> __device__ __forceinline__ double to_acc<double>(double v) { return v; }
+template <> __device__ __forceinline__ int32_t to_acc<int32_t>(int32_t v) { return v; }
+template <> __device__ __forceinline__ int64_t to_acc<int64_t>(int64_t v) { return v; }
 template <typename T> __device__ __forceinline__ T from_acc(typename Acc<T>::type v);
 template <> __device__ __forceinline__ __half from_acc<__half>(float v) { return __float2half(v); }
 template <> __device__ __forceinline__ __nv_bfloat16 from_acc<__nv_bfloat16>(float v) { return __float2bfloat16(v); }
 template <> __device__ __forceinline__ float from_acc<float>(float v) { return v; }
 template <> __device__ __forceinline__ double from_acc<double>(double v) { return v; }
+template <> __device__ __forceinline__ int32_t from_acc<int32_t>(int32_t v) { return v; }
+template <> __device__ __forceinline__ int64_t from_acc<int64_t>(int64_t v) { return v; }
 
 template <int OP, typename A>
 __device__ __forceinline__ A red_op(A a, A b) {

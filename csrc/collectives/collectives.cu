@@ -433,8 +433,8 @@ static ViewDev make_view(const dlbb_view_t* v) {
 static size_t dtype_size(int dt) {
     switch (dt) {
         case DLBB_F16: case DLBB_BF16: return 2;
-        case DLBB_F32: return 4;
-        case DLBB_F64: return 8;
+        case DLBB_F32: case DLBB_I32: return 4;
+        case DLBB_F64: case DLBB_I64: return 8;
         case DLBB_U8: return 1;
     }
     return 0;
@@ -474,6 +474,8 @@ static int launch_reduce(dlbb_comm* c, int dtype, int op, const void* src, void*
         case DLBB_BF16: return launch_reduce_op<__nv_bfloat16>(c, op, src, dst, extra, pack, view, red_off, red_n, bytes_hint, s);
         case DLBB_F32: return launch_reduce_op<float>(c, op, src, dst, extra, pack, view, red_off, red_n, bytes_hint, s);
         case DLBB_F64: return launch_reduce_op<double>(c, op, src, dst, extra, pack, view, red_off, red_n, bytes_hint, s);
+        case DLBB_I32: return launch_reduce_op<int32_t>(c, op, src, dst, extra, pack, view, red_off, red_n, bytes_hint, s);
+        case DLBB_I64: return launch_reduce_op<int64_t>(c, op, src, dst, extra, pack, view, red_off, red_n, bytes_hint, s);
     }
     set_error("reduction on unsupported dtype %d", dtype);
     return -2;
@@ -520,6 +522,8 @@ static int launch_twoshot(dlbb_comm* c, int dtype, int op, bool nvls, const void
         case DLBB_BF16: return launch_twoshot_op<__nv_bfloat16>(c, op, nvls, src, dst, extra, view, src_off, n, s);
         case DLBB_F32: return launch_twoshot_op<float>(c, op, nvls, src, dst, extra, view, src_off, n, s);
         case DLBB_F64: return launch_twoshot_op<double>(c, op, false, src, dst, extra, view, src_off, n, s);
+        case DLBB_I32: return launch_twoshot_op<int32_t>(c, op, false, src, dst, extra, view, src_off, n, s);
+        case DLBB_I64: return launch_twoshot_op<int64_t>(c, op, false, src, dst, extra, view, src_off, n, s);
     }
     set_error("reduction on unsupported dtype %d", dtype);
     return -2;
@@ -546,7 +550,7 @@ static int allreduce_impl(dlbb_comm* c, const void* in, void* out, const void* e
     const int64_t VE = 16 / (int64_t)es;
     const int64_t cap = static_cast<int64_t>(c->stage_bytes / es) / (VE * c->world) * (VE * c->world);
     const int64_t oneshot_max = c->oneshot_max ? (int64_t)c->oneshot_max : (c->world <= 2 ? (4 << 20) : (512 << 10));
-    const bool nvls_ok = dlbb_comm_has_multicast(c) && op == DLBB_SUM && dtype != DLBB_F64;
+    const bool nvls_ok = dlbb_comm_has_multicast(c) && op == DLBB_SUM && (dtype == DLBB_F16 || dtype == DLBB_BF16 || dtype == DLBB_F32);
     int64_t done = 0;
     while (done < count) {
         const int64_t left = count - done;

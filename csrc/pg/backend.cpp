@@ -1,0 +1,407 @@
+// torch.distributed process-group backend "dlbb" (also reachable as "ccl" through the
+// oneccl_bindings_for_pytorch shim): a c10d::Backend whose collectives are the hand-written
+// sm_100a kernels of libdlbb.so running over NVLink peer / multicast memory.
+//
+// Takes the place of oneCCL's c10d backend and of Gloo in the reference's DeepSpeed / torch paths
+// (collectives/1d/dsccl.py:47-163, collectives/3d/dsccl.py:34-118, test/test_deepseed.py:24-181,
+// test/ccl.py:24-57) and sits under the mpi4py shim (models.py:95, collectives/1d/openmpi.py).
+//
+//  * CUDA tensors: the kernel is enqueued on the caller's current stream; the returned Work
+//    carries a CUDA event (wait() = stream-side wait, like ProcessGroupNCCL).
+//  * CPU tensors (what the unchanged reference scripts create, e.g. collectives/1d/dsgloo.py:267):
+//    copied to the rank's GPU, reduced / moved there, copied back, complete on return - so the
+//    reference's host-clock timing brackets the whole operation.
+//  * point-to-point ops run on two private streams (one for sends, one for receives) so that a
+//    ring of isend / irecv cannot deadlock on issue order.
+#include <ATen/cuda/CUDAContext.h>
+#include <ATen/cuda/CUDAEvent.h>
+#include <c10/cuda/CUDAGuard.h>
+#include <c10/cuda/CUDAStream.h>
+#include <torch/csrc/distributed/c10d/Backend.hpp>
+#include <torch/csrc/distributed/c10d/Store.hpp>
+#include <torch/csrc/distributed/c10d/Types.hpp>
+#include <torch/csrc/distributed/c10d/Work.hpp>
+#include <torch/extension.h>
+#include <unistd.h>
+
+#include <chrono>
+#include <string>
+#include <vector>
+
+#include "../../include/dlbb.h"
+#include "../../include/dlbb_comm.h"
+
+namespace dlbb_pg {
+
+using c10d::Work;
+
+#define DLBB_CALL(expr)                                                                       \
+    do {                                                                                      \
+        int _rc = (expr);                                                                     \
+        TORCH_CHECK(_rc == 0, "dlbb backend: ", #expr, " failed (", _rc, "): ", dlbb_last_error()); \
+    } while (0)
+
+class WorkDlbb : public Work {
+  public:
+    WorkDlbb(c10d::OpType op, std::vector<at::Tensor> outputs, c10::optional<at::cuda::CUDAEvent> ev,
+             c10::DeviceIndex dev)
+        : Work(-1, op), outputs_(std::move(outputs)), event_(std::move(ev)), dev_(dev) {
+        future_ = c10::make_intrusive<at::ivalue::Future>(c10::ListType::create(c10::TensorType::get()));
+        future_->markCompleted(at::IValue(outputs_));
+    }
+    bool isCompleted() override { return !event_.has_value() || event_->query(); }
+    bool isSuccess() const override { return true; }
+    bool wait(std::chrono::milliseconds /*timeout*/ = kNoTimeout) override {
+        if (event_.has_value()) event_->block(c10::cuda::getCurrentCUDAStream(dev_));
+        return true;
+    }
+    void synchronize() override { wait(); }
+    std::vector<at::Tensor> result() override { return outputs_; }
+    c10::intrusive_ptr<c10::ivalue::Future> getFuture() override { return future_; }
+
+  private:
+    std::vector<at::Tensor> outputs_;
+    c10::optional<at::cuda::CUDAEvent> event_;
+    c10::DeviceIndex dev_;
+    c10::intrusive_ptr<at::ivalue::Future> future_;
+};
+
+static int to_dlbb_dtype(at::ScalarType t, bool reduce) {
+    switch (t) {
+        case at::kHalf: return DLBB_F16;
+        case at::kBFloat16: return DLBB_BF16;
+        case at::kFloat: return DLBB_F32;
+        case at::kDouble: return DLBB_F64;
+        case at::kInt: return DLBB_I32;
+        case at::kLong: return DLBB_I64;
+        default: break;
+    }
+    TORCH_CHECK(!reduce, "dlbb backend: reductions support fp16/bf16/fp32/fp64/int32/int64, got ", t);
+    return DLBB_U8;
+}
+
+static int to_dlbb_op(const c10d::ReduceOp& op) {
+    switch (op) {
+        case c10d::ReduceOp::SUM: case c10d::ReduceOp::AVG: return DLBB_SUM;
+        case c10d::ReduceOp::MAX: return DLBB_MAX;
+        case c10d::ReduceOp::MIN: return DLBB_MIN;
+        case c10d::ReduceOp::PRODUCT: return DLBB_PROD;
+        default: TORCH_CHECK(false, "dlbb backend: unsupported reduce op");
+    }
+    return DLBB_SUM;
+}
+
+class BackendDlbb : public c10d::Backend {
+  public:
+    BackendDlbb(const c10::intrusive_ptr<c10d::Store>& store, int rank, int size) : Backend(rank, size) {
+        dev_ = at::cuda::current_device();
+        // all ranks must name the same rendezvous: rank 0 publishes a unique id through the store
+        std::string job;
+        if (rank == 0) {
+            job = std::to_string(getpid()) + "-" + std::to_string(std::chrono::steady_clock::now().time_since_epoch().count());
+            store->set("dlbb_job", std::vector<uint8_t>(job.begin(), job.end()));
+        } else {
+            auto v = store->get("dlbb_job");
+            job.assign(v.begin(), v.end());
+        }
+        DLBB_CALL(dlbb_comm_create(rank, size, dev_, job.c_str(), 0, &comm_));
+    }
+    ~BackendDlbb() override { shutdown(); }
+    void shutdown() override {
+        if (comm_) {
+            cudaDeviceSynchronize();
+            dlbb_comm_destroy(comm_);
+            comm_ = nullptr;
+        }
+    }
+    const std::string getBackendName() const override { return "dlbb"; }
+    bool has_multicast() const { return dlbb_comm_has_multicast(comm_) != 0; }
+    void set_ctas(int n) { dlbb_comm_set_ctas(comm_, n); }
+    void set_oneshot_max_bytes(int64_t n) { dlbb_comm_set_oneshot_max_bytes(comm_, static_cast<size_t>(n)); }
+    void set_algo(int a) { algo_ = a; }
+
+    // ------------------------------------------------------------------ collectives
+    c10::intrusive_ptr<Work> allreduce(std::vector<at::Tensor>& tensors, const c10d::AllreduceOptions& opts) override {
+        TORCH_CHECK(tensors.size() == 1, "dlbb backend: one tensor per rank");
+        at::Tensor& t = tensors[0];
+        Staged s = stage_in(t, /*need_copy=*/true);
+        const int dt = to_dlbb_dtype(s.dev.scalar_type(), true);
+        if (s.dev.is_contiguous()) {
+            DLBB_CALL(dlbb_allreduce(comm_, s.dev.data_ptr(), s.dev.data_ptr(), s.dev.numel(), dt,
+                                     to_dlbb_op(opts.reduceOp), algo_, nullptr, stream()));
+        } else {
+            // strided view: gathered by the kernel itself (no .contiguous() pre-pass), result scattered back
+            TORCH_CHECK(s.dev.dim() <= 4, "dlbb backend: strided all_reduce supports up to 4 dims");
+            dlbb_view_t v{};
+            v.ndim = static_cast<int>(s.dev.dim());
+            for (int i = 0; i < v.ndim; ++i) { v.size[i] = s.dev.size(i); v.stride[i] = s.dev.stride(i); }
+            at::Tensor tmp = at::empty(s.dev.sizes(), s.dev.options());
+            DLBB_CALL(dlbb_allreduce(comm_, s.dev.data_ptr(), tmp.data_ptr(), s.dev.numel(), dt,
+                                     to_dlbb_op(opts.reduceOp), algo_, &v, stream()));
+            s.dev.copy_(tmp);
+        }
+        if (opts.reduceOp == c10d::ReduceOp::AVG) s.dev.div_(getSize());
+        return finish(c10d::OpType::ALLREDUCE, s, {t});
+    }
+
+    c10::intrusive_ptr<Work> broadcast(std::vector<at::Tensor>& tensors, const c10d::BroadcastOptions& opts) override {
+        TORCH_CHECK(tensors.size() == 1, "dlbb backend: one tensor per rank");
+        at::Tensor& t = tensors[0];
+        const int root = static_cast<int>(opts.rootRank);
+        Staged s = stage_in(t, getRank() == root, /*force_contig=*/true);
+        DLBB_CALL(dlbb_broadcast(comm_, s.dev.data_ptr(), nbytes(s.dev), DLBB_U8, root, stream()));
+        return finish(c10d::OpType::BROADCAST, s, {t});
+    }
+
+    c10::intrusive_ptr<Work> reduce(std::vector<at::Tensor>& tensors, const c10d::ReduceOptions& opts) override {
+        TORCH_CHECK(tensors.size() == 1, "dlbb backend: one tensor per rank");
+        at::Tensor& t = tensors[0];
+        const int root = static_cast<int>(opts.rootRank);
+        Staged s = stage_in(t, true, true);
+        DLBB_CALL(dlbb_reduce(comm_, s.dev.data_ptr(), s.dev.data_ptr(), s.dev.numel(),
+                              to_dlbb_dtype(s.dev.scalar_type(), true), to_dlbb_op(opts.reduceOp), root, stream()));
+        if (opts.reduceOp == c10d::ReduceOp::AVG && getRank() == root) s.dev.div_(getSize());
+        s.copy_back = s.copy_back && getRank() == root;
+        return finish(c10d::OpType::REDUCE, s, {t});
+    }
+
+    c10::intrusive_ptr<Work> _allgather_base(at::Tensor& out, at::Tensor& in, const c10d::AllgatherOptions&) override {
+        TORCH_CHECK(out.numel() == in.numel() * getSize(), "dlbb backend: all_gather_into_tensor size mismatch");
+        Staged si = stage_in(in, true, true);
+        Staged so = stage_in(out, false, true);
+        DLBB_CALL(dlbb_allgather(comm_, si.dev.data_ptr(), so.dev.data_ptr(), nbytes(si.dev), DLBB_U8, nullptr, stream()));
+        return finish(c10d::OpType::_ALLGATHER_BASE, so, {out});
+    }
+
+    c10::intrusive_ptr<Work> allgather(std::vector<std::vector<at::Tensor>>& outs, std::vector<at::Tensor>& ins,
+                                       const c10d::AllgatherOptions& opts) override {
+        TORCH_CHECK(ins.size() == 1 && outs.size() == 1 && (int)outs[0].size() == getSize(),
+                    "dlbb backend: all_gather expects one input and world_size outputs");
+        at::Tensor& in = ins[0];
+        Staged si = stage_in(in, true, true);
+        at::Tensor flat = at::empty({getSize(), in.numel()}, si.dev.options());
+        DLBB_CALL(dlbb_allgather(comm_, si.dev.data_ptr(), flat.data_ptr(), nbytes(si.dev), DLBB_U8, nullptr, stream()));
+        for (int p = 0; p < getSize(); ++p) outs[0][p].copy_(flat[p].view_as(in), /*non_blocking=*/false);
+        return done(c10d::OpType::ALLGATHER, outs[0], in.is_cuda());
+    }
+
+    c10::intrusive_ptr<Work> gather(std::vector<std::vector<at::Tensor>>& outs, std::vector<at::Tensor>& ins,
+                                    const c10d::GatherOptions& opts) override {
+        TORCH_CHECK(ins.size() == 1, "dlbb backend: gather expects one input");
+        const int root = static_cast<int>(opts.rootRank);
+        at::Tensor& in = ins[0];
+        Staged si = stage_in(in, true, true);
+        at::Tensor flat;
+        if (getRank() == root) {
+            TORCH_CHECK(outs.size() == 1 && (int)outs[0].size() == getSize(), "dlbb backend: gather needs world_size outputs on the root");
+            flat = at::empty({getSize(), in.numel()}, si.dev.options());
+        }
+        DLBB_CALL(dlbb_gather(comm_, si.dev.data_ptr(), flat.defined() ? flat.data_ptr() : nullptr, nbytes(si.dev), DLBB_U8,
+                              root, stream()));
+        std::vector<at::Tensor> res;
+        if (getRank() == root) {
+            for (int p = 0; p < getSize(); ++p) outs[0][p].copy_(flat[p].view_as(in));
+            res = outs[0];
+        }
+        return done(c10d::OpType::GATHER, res, in.is_cuda());
+    }
+
+    c10::intrusive_ptr<Work> scatter(std::vector<at::Tensor>& outs, std::vector<std::vector<at::Tensor>>& ins,
+                                     const c10d::ScatterOptions& opts) override {
+        TORCH_CHECK(outs.size() == 1, "dlbb backend: scatter expects one output");
+        const int root = static_cast<int>(opts.rootRank);
+        at::Tensor& out = outs[0];
+        Staged so = stage_in(out, false, true);
+        at::Tensor flat;
+        if (getRank() == root) {
+            TORCH_CHECK(ins.size() == 1 && (int)ins[0].size() == getSize(), "dlbb backend: scatter needs world_size inputs on the root");
+            flat = at::empty({getSize(), out.numel()}, so.dev.options());
+            for (int p = 0; p < getSize(); ++p) flat[p].copy_(ins[0][p].reshape({-1}));
+        }
+        DLBB_CALL(dlbb_scatter(comm_, flat.defined() ? flat.data_ptr() : nullptr, so.dev.data_ptr(), nbytes(so.dev), DLBB_U8,
+                               root, stream()));
+        return finish(c10d::OpType::SCATTER, so, {out});
+    }
+
+    c10::intrusive_ptr<Work> _reduce_scatter_base(at::Tensor& out, at::Tensor& in, const c10d::ReduceScatterOptions& opts) override {
+        TORCH_CHECK(in.numel() == out.numel() * getSize(), "dlbb backend: reduce_scatter_tensor size mismatch");
+        Staged si = stage_in(in, true, true);
+        Staged so = stage_in(out, false, true);
+        DLBB_CALL(dlbb_reduce_scatter(comm_, si.dev.data_ptr(), so.dev.data_ptr(), so.dev.numel(),
+                                      to_dlbb_dtype(si.dev.scalar_type(), true), to_dlbb_op(opts.reduceOp), stream()));
+        if (opts.reduceOp == c10d::ReduceOp::AVG) so.dev.div_(getSize());
+        return finish(c10d::OpType::_REDUCE_SCATTER_BASE, so, {out});
+    }
+
+    c10::intrusive_ptr<Work> reduce_scatter(std::vector<at::Tensor>& outs, std::vector<std::vector<at::Tensor>>& ins,
+                                            const c10d::ReduceScatterOptions& opts) override {
+        TORCH_CHECK(outs.size() == 1 && ins.size() == 1 && (int)ins[0].size() == getSize(),
+                    "dlbb backend: reduce_scatter expects one output and world_size inputs");
+        at::Tensor& out = outs[0];
+        Staged so = stage_in(out, false, true);
+        at::Tensor flat = at::empty({getSize(), out.numel()}, so.dev.options());
+        for (int p = 0; p < getSize(); ++p) flat[p].copy_(ins[0][p].reshape({-1}));
+        DLBB_CALL(dlbb_reduce_scatter(comm_, flat.data_ptr(), so.dev.data_ptr(), so.dev.numel(),
+                                      to_dlbb_dtype(so.dev.scalar_type(), true), to_dlbb_op(opts.reduceOp), stream()));
+        if (opts.reduceOp == c10d::ReduceOp::AVG) so.dev.div_(getSize());
+        return finish(c10d::OpType::REDUCE_SCATTER, so, {out});
+    }
+
+    c10::intrusive_ptr<Work> alltoall_base(at::Tensor& out, at::Tensor& in, std::vector<int64_t>& osplit,
+                                           std::vector<int64_t>& isplit, const c10d::AllToAllOptions&) override {
+        TORCH_CHECK(osplit.empty() && isplit.empty(), "dlbb backend: all_to_all_single supports equal splits only");
+        TORCH_CHECK(in.numel() == out.numel() && in.numel() % getSize() == 0, "dlbb backend: all_to_all size mismatch");
+        Staged si = stage_in(in, true, true);
+        Staged so = stage_in(out, false, true);
+        DLBB_CALL(dlbb_alltoall(comm_, si.dev.data_ptr(), so.dev.data_ptr(), nbytes(si.dev) / getSize(), DLBB_U8, stream()));
+        return finish(c10d::OpType::ALLTOALL_BASE, so, {out});
+    }
+
+    c10::intrusive_ptr<Work> alltoall(std::vector<at::Tensor>& outs, std::vector<at::Tensor>& ins,
+                                      const c10d::AllToAllOptions&) override {
+        TORCH_CHECK((int)outs.size() == getSize() && (int)ins.size() == getSize(), "dlbb backend: all_to_all needs world_size tensors");
+        const int64_t n = ins[0].numel();
+        for (int p = 0; p < getSize(); ++p)
+            TORCH_CHECK(ins[p].numel() == n && outs[p].numel() == n, "dlbb backend: all_to_all supports equal chunk sizes only");
+        const bool cuda = ins[0].is_cuda();
+        auto options = ins[0].options().device(c10::Device(c10::kCUDA, dev_));
+        at::Tensor fin = at::empty({getSize(), n}, options), fout = at::empty({getSize(), n}, options);
+        for (int p = 0; p < getSize(); ++p) fin[p].copy_(ins[p].reshape({-1}));
+        DLBB_CALL(dlbb_alltoall(comm_, fin.data_ptr(), fout.data_ptr(), n * ins[0].element_size(), DLBB_U8, stream()));
+        for (int p = 0; p < getSize(); ++p) outs[p].copy_(fout[p].view_as(outs[p]));
+        return done(c10d::OpType::ALLTOALL, outs, cuda);
+    }
+
+    // ------------------------------------------------------------------ point to point
+    c10::intrusive_ptr<Work> send(std::vector<at::Tensor>& tensors, int dst, int /*tag*/) override {
+        TORCH_CHECK(tensors.size() == 1, "dlbb backend: one tensor per send");
+        return p2p(tensors[0], dst, /*is_send=*/true);
+    }
+    c10::intrusive_ptr<Work> recv(std::vector<at::Tensor>& tensors, int src, int /*tag*/) override {
+        TORCH_CHECK(tensors.size() == 1, "dlbb backend: one tensor per recv");
+        return p2p(tensors[0], src, /*is_send=*/false);
+    }
+
+    c10::intrusive_ptr<Work> barrier(const c10d::BarrierOptions&) override {
+        c10::cuda::CUDAGuard g(dev_);
+        DLBB_CALL(dlbb_barrier(comm_, stream()));
+        // host-blocking, like an MPI barrier: the reference brackets its timed regions with it
+        C10_CUDA_CHECK(cudaStreamSynchronize(c10::cuda::getCurrentCUDAStream(dev_)));
+        return c10::make_intrusive<WorkDlbb>(c10d::OpType::BARRIER, std::vector<at::Tensor>{}, c10::nullopt, dev_);
+    }
+
+  private:
+    struct Staged {
+        at::Tensor dev;        // tensor the kernel works on (the original if it already lives on the GPU)
+        at::Tensor host;       // original CPU tensor (undefined for CUDA inputs)
+        at::Tensor orig;       // original CUDA tensor when a contiguous copy had to be made
+        bool copy_back = false;
+    };
+
+    void* stream() { return c10::cuda::getCurrentCUDAStream(dev_).stream(); }
+    static int64_t nbytes(const at::Tensor& t) { return t.numel() * t.element_size(); }
+
+    // Bring a tensor to the GPU (CPU callers) and, when the op needs it, make it dense.
+    Staged stage_in(at::Tensor& t, bool need_copy, bool force_contig = false) {
+        Staged s;
+        c10::cuda::CUDAGuard g(dev_);
+        if (t.is_cuda()) {
+            TORCH_CHECK(t.get_device() == dev_, "dlbb backend: tensor is on cuda:", t.get_device(), " but this rank drives cuda:", (int)dev_);
+            if (force_contig && !t.is_contiguous()) {
+                s.orig = t;
+                s.dev = need_copy ? t.contiguous() : at::empty(t.sizes(), t.options());
+                s.copy_back = true;
+            } else {
+                s.dev = t;
+            }
+        } else {
+            s.host = t;
+            auto opt = t.options().device(c10::Device(c10::kCUDA, dev_));
+            s.dev = need_copy ? t.contiguous().to(opt.device(), /*non_blocking=*/false) : at::empty(t.sizes(), opt);
+            s.copy_back = true;
+        }
+        return s;
+    }
+
+    c10::intrusive_ptr<Work> finish(c10d::OpType op, Staged& s, std::vector<at::Tensor> outs) {
+        if (s.host.defined()) {
+            if (s.copy_back) s.host.copy_(s.dev);  // synchronous D2H: the op is complete on return
+            else C10_CUDA_CHECK(cudaStreamSynchronize(c10::cuda::getCurrentCUDAStream(dev_)));
+            return c10::make_intrusive<WorkDlbb>(op, std::move(outs), c10::nullopt, dev_);
+        }
+        if (s.orig.defined() && s.copy_back) s.orig.copy_(s.dev);
+        return done(op, std::move(outs), true);
+    }
+
+    c10::intrusive_ptr<Work> done(c10d::OpType op, std::vector<at::Tensor> outs, bool cuda) {
+        if (!cuda) {
+            C10_CUDA_CHECK(cudaStreamSynchronize(c10::cuda::getCurrentCUDAStream(dev_)));
+            return c10::make_intrusive<WorkDlbb>(op, std::move(outs), c10::nullopt, dev_);
+        }
+        at::cuda::CUDAEvent ev;
+        ev.record(c10::cuda::getCurrentCUDAStream(dev_));
+        return c10::make_intrusive<WorkDlbb>(op, std::move(outs), std::move(ev), dev_);
+    }
+
+    c10::intrusive_ptr<Work> p2p(at::Tensor& t, int peer, bool is_send) {
+        TORCH_CHECK(peer >= 0 && peer < getSize() && peer != getRank(), "dlbb backend: bad p2p peer ", peer);
+        c10::cuda::CUDAGuard g(dev_);
+        if (!p2p_streams_) {
+            send_stream_ = c10::cuda::getStreamFromPool(false, dev_);
+            recv_stream_ = c10::cuda::getStreamFromPool(false, dev_);
+            p2p_streams_ = true;
+        }
+        auto& side = is_send ? *send_stream_ : *recv_stream_;
+        const bool cpu = !t.is_cuda();
+        at::Tensor devt;
+        if (cpu) devt = is_send ? t.contiguous().to(c10::Device(c10::kCUDA, dev_)) : at::empty(t.sizes(), t.options().device(c10::Device(c10::kCUDA, dev_)));
+        else {
+            TORCH_CHECK(t.is_contiguous(), "dlbb backend: p2p tensors must be contiguous");
+            devt = t;
+        }
+        // the side stream starts after everything already queued on the caller's stream
+        at::cuda::CUDAEvent before;
+        before.record(c10::cuda::getCurrentCUDAStream(dev_));
+        before.block(side);
+        const int64_t nb = nbytes(devt);
+        if (is_send) DLBB_CALL(dlbb_sendrecv(comm_, devt.data_ptr(), nb, peer, nullptr, 0, -1, DLBB_U8, side.stream()));
+        else DLBB_CALL(dlbb_sendrecv(comm_, nullptr, 0, -1, devt.data_ptr(), nb, peer, DLBB_U8, side.stream()));
+        c10::cuda::CUDACachingAllocator::recordStream(devt.storage().data_ptr(), side);
+        if (cpu) {
+            C10_CUDA_CHECK(cudaStreamSynchronize(side.stream()));
+            if (!is_send) t.copy_(devt);
+            return c10::make_intrusive<WorkDlbb>(is_send ? c10d::OpType::SEND : c10d::OpType::RECV,
+                                                 std::vector<at::Tensor>{t}, c10::nullopt, dev_);
+        }
+        at::cuda::CUDAEvent ev;
+        ev.record(side);
+        return c10::make_intrusive<WorkDlbb>(is_send ? c10d::OpType::SEND : c10d::OpType::RECV,
+                                             std::vector<at::Tensor>{t}, std::move(ev), dev_);
+    }
+
+    dlbb_comm_t* comm_ = nullptr;
+    c10::DeviceIndex dev_ = 0;
+    int algo_ = DLBB_ALGO_AUTO;
+    bool p2p_streams_ = false;
+    c10::optional<c10::cuda::CUDAStream> send_stream_, recv_stream_;
+};
+
+}  // namespace dlbb_pg
+
+PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
+    namespace py = pybind11;
+    using dlbb_pg::BackendDlbb;
+    m.doc() = "dlbb process-group backend (c10d::Backend over libdlbb.so)";
+    py::class_<BackendDlbb, c10d::Backend, c10::intrusive_ptr<BackendDlbb>>(m, "BackendDlbb")
+        .def("has_multicast", &BackendDlbb::has_multicast)
+        .def("set_ctas", &BackendDlbb::set_ctas)
+        .def("set_oneshot_max_bytes", &BackendDlbb::set_oneshot_max_bytes)
+        .def("set_algo", &BackendDlbb::set_algo);
+    m.def(
+        "create_backend",
+        [](const c10::intrusive_ptr<c10d::Store>& store, int rank, int size, const std::chrono::milliseconds&) {
+            return c10::make_intrusive<BackendDlbb>(store, rank, size);
+        },
+        py::arg("store"), py::arg("rank"), py::arg("size"), py::arg("timeout") = std::chrono::milliseconds(0),
+        py::call_guard<py::gil_scoped_release>());
+}

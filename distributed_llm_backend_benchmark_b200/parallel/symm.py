@@ -17,7 +17,8 @@ from .. import _lib
 
 VP, I, I64, F, SZ = C.c_void_p, C.c_int, C.c_int64, C.c_float, C.c_size_t
 
-DTYPES = {torch.float16: 0, torch.bfloat16: 1, torch.float32: 2, torch.float64: 3, torch.uint8: 4, torch.int8: 4}
+DTYPES = {torch.float16: 0, torch.bfloat16: 1, torch.float32: 2, torch.float64: 3, torch.uint8: 4, torch.int8: 4,
+          torch.int32: 5, torch.int64: 6}
 OPS = {"sum": 0, "max": 1, "min": 2, "prod": 3}
 ALGOS = {"auto": 0, "oneshot": 1, "twoshot": 2, "nvls": 3}
 

@@ -96,7 +96,7 @@ int dlbb_copy2d(const void* src, int64_t ld_src, void* dst, int64_t ld_dst, int 
                 void* stream);
 /* dtype conversion between fp16/bf16/fp32/fp64 (ref models.py:84,98; collectives/3d/openmpi.py:43).
  * dtype codes: DLBB_F16, DLBB_BF16, DLBB_F32, DLBB_F64. */
-enum { DLBB_F16 = 0, DLBB_BF16 = 1, DLBB_F32 = 2, DLBB_F64 = 3, DLBB_U8 = 4 };
+enum { DLBB_F16 = 0, DLBB_BF16 = 1, DLBB_F32 = 2, DLBB_F64 = 3, DLBB_U8 = 4, DLBB_I32 = 5, DLBB_I64 = 6 };
 int dlbb_cast(const void* src, int src_dtype, void* dst, int dst_dtype, int64_t n, void* stream);
 
 /* ------------------------------------------------------------------------------------------
