@@ -55,5 +55,6 @@ struct dlbb_comm {
     unsigned parity = 0;           // alternates the staging half used by single-barrier kernels
     int ctas = 0;                  // 0 = auto
     size_t oneshot_max = 0;        // 0 = auto
+    int default_algo = 0;          // DLBB_ALGO: what DLBB_ALGO_AUTO resolves to (0 = size-based choice)
     dlbb::CommDev dev{};
 };

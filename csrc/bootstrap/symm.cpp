@@ -350,6 +350,12 @@ int dlbb_comm_create(int rank, int world, int device, const char* job, size_t st
     if (e) c->ctas = atoi(e);
     e = getenv("DLBB_ONESHOT_MAX_BYTES");
     if (e) c->oneshot_max = static_cast<size_t>(atol(e));
+    e = getenv("DLBB_ALGO");   // analogue of CCL_ALLREDUCE (collectives/3d/launch_dsccl.sh:46)
+    if (e) {
+        const std::string a(e);
+        c->default_algo = a == "oneshot" ? DLBB_ALGO_ONESHOT : a == "twoshot" ? DLBB_ALGO_TWOSHOT
+                        : a == "nvls" ? DLBB_ALGO_NVLS : DLBB_ALGO_AUTO;
+    }
     if (getenv("DLBB_LOG_LEVEL") && rank == 0)
         fprintf(stderr, "dlbb: comm up, %d ranks, granularity %zu MiB, staging 2x%zu MiB, multicast %s\n", world,
                 c->gran >> 20, c->stage_bytes >> 20, c->mc_supported ? "on" : "off");

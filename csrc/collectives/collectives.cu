@@ -547,6 +547,7 @@ static int allreduce_impl(dlbb_comm* c, const void* in, void* out, const void* e
     DLBB_REQUIRE(count >= 0, "allreduce: negative count");
     if (count == 0) return 0;
     const ViewDev view = make_view(in_view);
+    if (algo == DLBB_ALGO_AUTO) algo = c->default_algo;
     const int64_t VE = 16 / (int64_t)es;
     const int64_t cap = static_cast<int64_t>(c->stage_bytes / es) / (VE * c->world) * (VE * c->world);
     const int64_t oneshot_max = c->oneshot_max ? (int64_t)c->oneshot_max : (c->world <= 2 ? (4 << 20) : (512 << 10));
