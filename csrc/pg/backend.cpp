@@ -22,9 +22,11 @@
 #include <torch/csrc/distributed/c10d/Types.hpp>
 #include <torch/csrc/distributed/c10d/Work.hpp>
 #include <torch/extension.h>
+#include <pybind11/chrono.h>
 #include <unistd.h>
 
 #include <chrono>
+#include <functional>
 #include <string>
 #include <vector>
 
@@ -43,16 +45,29 @@ using c10d::Work;
 
 class WorkDlbb : public Work {
   public:
+    // host_blocking: wait() blocks the calling thread (CPU-tensor semantics) instead of only ordering
+    // the current stream; on_wait runs once after completion (device -> host copy of a received tensor).
     WorkDlbb(c10d::OpType op, std::vector<at::Tensor> outputs, c10::optional<at::cuda::CUDAEvent> ev,
-             c10::DeviceIndex dev)
-        : Work(-1, op), outputs_(std::move(outputs)), event_(std::move(ev)), dev_(dev) {
+             c10::DeviceIndex dev, bool host_blocking = false, std::function<void()> on_wait = nullptr,
+             std::vector<at::Tensor> keep_alive = {})
+        : Work(-1, op), outputs_(std::move(outputs)), event_(std::move(ev)), dev_(dev), host_blocking_(host_blocking),
+          on_wait_(std::move(on_wait)), keep_alive_(std::move(keep_alive)) {
         future_ = c10::make_intrusive<at::ivalue::Future>(c10::ListType::create(c10::TensorType::get()));
         future_->markCompleted(at::IValue(outputs_));
     }
     bool isCompleted() override { return !event_.has_value() || event_->query(); }
     bool isSuccess() const override { return true; }
     bool wait(std::chrono::milliseconds /*timeout*/ = kNoTimeout) override {
-        if (event_.has_value()) event_->block(c10::cuda::getCurrentCUDAStream(dev_));
+        if (event_.has_value()) {
+            if (host_blocking_) event_->synchronize();
+            else event_->block(c10::cuda::getCurrentCUDAStream(dev_));
+        }
+        if (on_wait_) {
+            auto fn = std::move(on_wait_);
+            on_wait_ = nullptr;
+            fn();
+        }
+        keep_alive_.clear();
         return true;
     }
     void synchronize() override { wait(); }
@@ -63,6 +78,9 @@ class WorkDlbb : public Work {
     std::vector<at::Tensor> outputs_;
     c10::optional<at::cuda::CUDAEvent> event_;
     c10::DeviceIndex dev_;
+    bool host_blocking_;
+    std::function<void()> on_wait_;
+    std::vector<at::Tensor> keep_alive_;
     c10::intrusive_ptr<at::ivalue::Future> future_;
 };
 
@@ -367,16 +385,23 @@ class BackendDlbb : public c10d::Backend {
         if (is_send) DLBB_CALL(dlbb_sendrecv(comm_, devt.data_ptr(), nb, peer, nullptr, 0, -1, DLBB_U8, side.stream()));
         else DLBB_CALL(dlbb_sendrecv(comm_, nullptr, 0, -1, devt.data_ptr(), nb, peer, DLBB_U8, side.stream()));
         c10::cuda::CUDACachingAllocator::recordStream(devt.storage().data_ptr(), side);
-        if (cpu) {
-            C10_CUDA_CHECK(cudaStreamSynchronize(side.stream()));
-            if (!is_send) t.copy_(devt);
-            return c10::make_intrusive<WorkDlbb>(is_send ? c10d::OpType::SEND : c10d::OpType::RECV,
-                                                 std::vector<at::Tensor>{t}, c10::nullopt, dev_);
-        }
         at::cuda::CUDAEvent ev;
         ev.record(side);
-        return c10::make_intrusive<WorkDlbb>(is_send ? c10d::OpType::SEND : c10d::OpType::RECV,
-                                             std::vector<at::Tensor>{t}, std::move(ev), dev_);
+        const auto op = is_send ? c10d::OpType::SEND : c10d::OpType::RECV;
+        if (cpu) {
+            // asynchronous for host tensors too: the kernel may have to wait for the peer (a second
+            // message to the same rank needs the first to be consumed), and blocking here would
+            // deadlock two ranks that both isend before they irecv.  wait() blocks and, for a
+            // receive, copies the payload back to the host tensor.
+            std::function<void()> fin = nullptr;
+            if (!is_send) {
+                at::Tensor host = t, dev_copy = devt;
+                fin = [host, dev_copy]() mutable { host.copy_(dev_copy); };
+            }
+            return c10::make_intrusive<WorkDlbb>(op, std::vector<at::Tensor>{t}, std::move(ev), dev_, /*host_blocking=*/true,
+                                                 std::move(fin), std::vector<at::Tensor>{devt});
+        }
+        return c10::make_intrusive<WorkDlbb>(op, std::vector<at::Tensor>{t}, std::move(ev), dev_);
     }
 
     dlbb_comm_t* comm_ = nullptr;

