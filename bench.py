@@ -223,6 +223,9 @@ def main() -> None:
         }
         if reduced:
             out["INVALID"] = "reduced layer count (debug run)"
+        if os.environ.get("DLBB_DEBUG_SKIP_OPT") == "1":
+            out["INVALID"] = "optimizer skipped (debug run)"
+        out["env"] = {k: v for k, v in os.environ.items() if k.startswith("DLBB_")}
         print(json.dumps(out), flush=True)
     if world > 1:
         dist.barrier()

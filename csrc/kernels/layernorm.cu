@@ -24,6 +24,18 @@ __device__ __forceinline__ float block_sum(float v, float* sh) {
     return warp_sum(t);
 }
 
+// Two sums at once: half the barriers of two block_sum calls (the backward needs both per row).
+__device__ __forceinline__ float2 block_sum2(float a, float b, float2* sh) {
+    a = warp_sum(a);
+    b = warp_sum(b);
+    const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+    __syncthreads();
+    if (l == 0) sh[w] = make_float2(a, b);
+    __syncthreads();
+    float2 t = (l < kLnThreads / 32) ? sh[l] : make_float2(0.f, 0.f);
+    return make_float2(warp_sum(t.x), warp_sum(t.y));
+}
+
 // ---------------------------------------------------------------- vector path (cols % 8 == 0)
 template <int VPT>
 __global__ void __launch_bounds__(kLnThreads)
@@ -93,7 +105,7 @@ ln_bwd_vec_kernel(const uint4* __restrict__ dy, const uint4* __restrict__ x,
                   const float* __restrict__ mean, const float* __restrict__ rstd,
                   const uint4* __restrict__ gamma, const uint4* __restrict__ dres,
                   uint4* __restrict__ dx, float* __restrict__ partials, int rows, int cols) {
-    __shared__ float sh[32];
+    __shared__ float2 sh2[32];
     const int nvec = cols >> 3;
     float pg[VPT][8], pb[VPT][8];  // per-thread column partials of dgamma / dbeta
     float gam[VPT][8];
@@ -140,8 +152,8 @@ ln_bwd_vec_kernel(const uint4* __restrict__ dy, const uint4* __restrict__ x,
                 for (int j = 0; j < 8; ++j) { xh[i][j] = 0.f; g[i][j] = 0.f; }
             }
         }
-        const float c1 = block_sum(s1, sh) / cols;
-        const float c2 = block_sum(s2, sh) / cols;
+        const float2 cs = block_sum2(s1, s2, reinterpret_cast<float2*>(sh2));
+        const float c1 = cs.x / cols, c2 = cs.y / cols;
         uint4* dxr = dx + (size_t)row * nvec;
 #pragma unroll
         for (int i = 0; i < VPT; ++i) {
@@ -243,18 +255,31 @@ ln_bwd_generic_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16*
     }
 }
 
-// Fold the per-CTA partials: one thread per column, coalesced across the CTA dimension.
-__global__ void ln_bwd_reduce_kernel(const float* __restrict__ partials, float* __restrict__ dgamma,
-                                     float* __restrict__ dbeta, int nparts, int cols) {
-    const int c = blockIdx.x * blockDim.x + threadIdx.x;
-    if (c >= cols) return;
+// Fold the per-CTA partials.  A 256-thread block owns 32 columns: lane = column, warp = slice of the
+// partial rows (8 slices), so every load is a coalesced 128 B line and 8 loads per column are in flight
+// at once; the slices are combined through shared memory in a fixed order (deterministic).
+__global__ void __launch_bounds__(256)
+ln_bwd_reduce_kernel(const float* __restrict__ partials, float* __restrict__ dgamma, float* __restrict__ dbeta,
+                     int nparts, int cols) {
+    __shared__ float sg[8][33], sb[8][33];
+    const int lane = threadIdx.x & 31, slice = threadIdx.x >> 5;
+    const int c = blockIdx.x * 32 + lane;
     float g = 0.f, b = 0.f;
-    for (int p = 0; p < nparts; ++p) {
-        g += partials[(size_t)p * 2 * cols + c];
-        b += partials[(size_t)p * 2 * cols + cols + c];
+    if (c < cols) {
+        for (int p = slice; p < nparts; p += 8) {
+            g += partials[(size_t)p * 2 * cols + c];
+            b += partials[(size_t)p * 2 * cols + cols + c];
+        }
     }
-    if (dgamma) dgamma[c] = g;
-    if (dbeta) dbeta[c] = b;
+    sg[slice][lane] = g;
+    sb[slice][lane] = b;
+    __syncthreads();
+    if (slice == 0 && c < cols) {
+#pragma unroll
+        for (int k = 1; k < 8; ++k) { g += sg[k][lane]; b += sb[k][lane]; }
+        if (dgamma) dgamma[c] = g;
+        if (dbeta) dbeta[c] = b;
+    }
 }
 
 static int ln_bwd_parts(int rows) {
@@ -265,7 +290,7 @@ static int ln_bwd_parts(int rows) {
             cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess)
             sms = 148;
     }
-    return rows < 2 * sms ? rows : 2 * sms;
+    return rows < 4 * sms ? rows : 4 * sms;
 }
 
 }  // namespace dlbb
@@ -333,7 +358,7 @@ int dlbb_layernorm_bwd(const void* dy, const void* x, const float* mean, const f
     }
     DLBB_CHECK_LAUNCH("layernorm_bwd");
     if (dgamma || dbeta) {
-        ln_bwd_reduce_kernel<<<(cols + 255) / 256, 256, 0, s>>>(partials, dgamma, dbeta, parts, cols);
+        ln_bwd_reduce_kernel<<<(cols + 31) / 32, 256, 0, s>>>(partials, dgamma, dbeta, parts, cols);
         DLBB_CHECK_LAUNCH("layernorm_bwd_reduce");
     }
     return 0;
@@ -442,7 +467,7 @@ extern "C" int dlbb_layernorm_bwd_noalloc(const void* dy, const void* x, const f
     }
     DLBB_CHECK_LAUNCH("layernorm_bwd_noalloc");
     if (dgamma || dbeta) {
-        ln_bwd_reduce_kernel<<<(cols + 255) / 256, 256, 0, s>>>(partials, dgamma, dbeta, parts, cols);
+        ln_bwd_reduce_kernel<<<(cols + 31) / 32, 256, 0, s>>>(partials, dgamma, dbeta, parts, cols);
         DLBB_CHECK_LAUNCH("layernorm_bwd_noalloc_reduce");
     }
     return 0;

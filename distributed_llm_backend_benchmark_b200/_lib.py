@@ -45,6 +45,7 @@ _SIGNATURES = {
     "dlbb_adam_f32": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_float, c_float, c_float,
                               c_float, c_float, c_float, c_int, c_void_p]),
     "dlbb_fill_u32": (c_int, [c_void_p, c_uint32, c_int64, c_void_p]),
+    "dlbb_adam_set_max_ctas": (None, [c_int]),
 }
 
 # Optional symbols (collectives / bootstrap) are bound lazily by parallel/symm.py through bind().

@@ -31,7 +31,14 @@ class DataParallelTrainer:
         self.step_count = 0
         dev = engine.device
         self.cuda = dev.type == "cuda"
-        self.overlap = overlap and self.cuda
+        import os as _os
+        # Overlap pays when the bucket kernel also communicates (world > 1: NVLink time hides under the
+        # backward GEMMs).  On one GPU the optimizer and the GEMMs compete for the same HBM bandwidth and
+        # power budget and co-running gains nothing (profiles/optimizer_overlap.md), so it runs after backward.
+        default_overlap = "1" if (comm is not None and comm.world_size > 1) else "0"
+        self.overlap = overlap and self.cuda and _os.environ.get("DLBB_DP_OVERLAP", default_overlap) == "1"
+        self._overlap_ctas = int(_os.environ.get("DLBB_ADAM_OVERLAP_CTAS", "148"))
+        self.skip_optimizer = _os.environ.get("DLBB_DEBUG_SKIP_OPT", "0") == "1"   # debugging aid, invalidates results
         self.buckets = engine.bucket_slices()
         # Optimizer state is sharded: rank r owns elements [r*shard, (r+1)*shard) of every bucket
         # (buckets are padded up to a multiple of world*8 elements on the comm side).
@@ -57,7 +64,10 @@ class DataParallelTrainer:
             self.state_off.append(o)
             o += n
         if self.cuda:
-            self.side = torch.cuda.Stream(device=dev, priority=-1)
+            # low priority: at every GEMM kernel boundary the GEMM's CTAs are placed first and the
+            # optimizer fills what is left (one small CTA per SM beside the resident GEMM CTA)
+            self.side = torch.cuda.Stream(device=dev, priority=0)
+            self.sm_count = torch.cuda.get_device_properties(dev).multi_processor_count
             self.ready = [torch.cuda.Event() for _ in self.buckets]
             self.done = torch.cuda.Event()
         if comm is not None:
@@ -72,6 +82,8 @@ class DataParallelTrainer:
 
     # ------------------------------------------------------------------ optimizer on one bucket
     def _update_bucket(self, i: int) -> None:
+        if self.skip_optimizer:
+            return
         eng = self.engine
         off, n = self.buckets[i]
         soff, sn = self.shards[i]
@@ -92,9 +104,17 @@ class DataParallelTrainer:
             return
         cur = torch.cuda.current_stream(self.engine.device)
         self.ready[i].record(cur)
+        last = i == len(self.buckets) - 1
         with torch.cuda.stream(self.side):
             self.side.wait_event(self.ready[i])
-            self._update_bucket(i)
+            if self.comm is None or self.world == 1:
+                from .. import _lib
+                # while backward is still running: one CTA per SM; the final bucket has the GPU to itself
+                _lib.load().dlbb_adam_set_max_ctas(0 if last else int(self._overlap_ctas))
+                self._update_bucket(i)
+                _lib.load().dlbb_adam_set_max_ctas(0)
+            else:
+                self._update_bucket(i)
 
     # ------------------------------------------------------------------ public step
     def step(self, x: torch.Tensor, target: torch.Tensor) -> torch.Tensor:

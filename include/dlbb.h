@@ -120,6 +120,10 @@ int dlbb_mse_loss(const void* y, const void* target, void* dy, float* loss, void
 int dlbb_adam_bf16(void* param, const void* grad, float* m, float* v, float* master, int64_t n,
                    float lr, float beta1, float beta2, float eps, float weight_decay,
                    float grad_scale, int step, void* stream);
+/* Cap the grid of the Adam kernels (0 = default).  With at most one 128-thread CTA per SM the update
+ * co-resides with a running persistent GEMM instead of displacing it (used by the DP engine while the
+ * backward pass is still in flight). */
+void dlbb_adam_set_max_ctas(int n);
 /* fp32 parameter variant for the toy DeepSpeed-style models (ref test/ds_mpi_test.py:8). */
 int dlbb_adam_f32(float* param, const float* grad, float* m, float* v, int64_t n, float lr,
                   float beta1, float beta2, float eps, float weight_decay, float grad_scale,

@@ -96,18 +96,20 @@ try:
                 if rank == root: check(f"reduce_{dn}_{n}", o, sum(v.double() for v in xs).to(dtype), tol)
             # ring sendrecv + plain send/recv
             nxt, prv = (rank + 1) % world, (rank - 1) % world
-            out = torch.empty(n, dtype=dtype, device=dev); comm.sendrecv(xs[rank], nxt, out, prv)
-            check(f"sendrecv_{dn}_{n}", out, xs[prv])
-            if rank == 0: comm.send(xs[0], 1)
-            elif rank == 1:
-                out = torch.empty(n, dtype=dtype, device=dev); comm.recv(out, 0); check(f"send_recv_{dn}_{n}", out, xs[0])
+            if world > 1:
+                out = torch.empty(n, dtype=dtype, device=dev); comm.sendrecv(xs[rank], nxt, out, prv)
+                check(f"sendrecv_{dn}_{n}", out, xs[prv])
+                if rank == 0: comm.send(xs[0], 1)
+                elif rank == 1:
+                    out = torch.empty(n, dtype=dtype, device=dev); comm.recv(out, 0); check(f"send_recv_{dn}_{n}", out, xs[0])
     # a message larger than the staging region (chunked inside the call)
     n = (80 << 20) // 2 + 1032
     xs = [gen(r, n, torch.bfloat16, seed=11) for r in range(world)]
     x = xs[rank].clone(); comm.all_reduce(x); check("allreduce_big_bf16", x, sum(v.double() for v in xs).to(torch.bfloat16), 2e-2)
     out = torch.empty(world * n, dtype=torch.bfloat16, device=dev); comm.all_gather(xs[rank], out); check("allgather_big", out, torch.cat(xs))
-    out = torch.empty(n, dtype=torch.bfloat16, device=dev); comm.sendrecv(xs[rank], (rank + 1) % world, out, (rank - 1) % world)
-    check("sendrecv_big", out, xs[(rank - 1) % world])
+    if world > 1:
+        out = torch.empty(n, dtype=torch.bfloat16, device=dev); comm.sendrecv(xs[rank], (rank + 1) % world, out, (rank - 1) % world)
+        check("sendrecv_big", out, xs[(rank - 1) % world])
     del xs, x, out
     torch.cuda.synchronize()
 
