@@ -11,7 +11,7 @@
 
 namespace dlbb {
 
-constexpr int kMaxCtas = 128;         // channels: one signal-pad row per CTA of a collective kernel
+constexpr int kMaxCtas = 160;         // channels: one signal-pad row per CTA of a collective kernel
 constexpr int kPadStride = DLBB_MAX_RANKS;  // uint32 slots per row
 // Signal pad layout (uint32 words): [kMaxCtas rows][kPadStride] for kernel barriers, then
 // a second bank of the same shape for the fused DP kernel (it runs on a side stream concurrently
@@ -19,6 +19,9 @@ constexpr int kPadStride = DLBB_MAX_RANKS;  // uint32 slots per row
 constexpr int kPadWordsPerBank = kMaxCtas * kPadStride;
 constexpr int kPadBanks = 4;          // 0: collectives, 1: fused DP kernel, 2: fused GEMM+all-reduce, 3: point-to-point
 constexpr size_t kPadBytes = sizeof(uint32_t) * kPadWordsPerBank * kPadBanks;
+// Per-tile arrival flags of the fused GEMM + all-reduce: [tile][source rank], epoch valued.
+constexpr size_t kMaxFusedTiles = 16384;
+constexpr size_t kTileFlagBytes = sizeof(uint32_t) * kMaxFusedTiles * DLBB_MAX_RANKS;
 
 struct Segment {
     bool live = false;
@@ -37,6 +40,7 @@ struct CommDev {
     char* stage[DLBB_MAX_RANKS];
     char* stage_mc;       // multicast mapping of the staging segment (nullptr if unavailable)
     uint32_t* pads_mc;
+    uint32_t* tile_flags[DLBB_MAX_RANKS];
 };
 
 }  // namespace dlbb
@@ -47,7 +51,7 @@ struct dlbb_comm {
     std::vector<dlbb::Segment> segs;
     bool mc_supported = false;
     size_t gran = 2u << 20;
-    int pad_seg = -1, stage_seg = -1;
+    int pad_seg = -1, stage_seg = -1, flag_seg = -1;
     size_t stage_bytes = 0;        // bytes of each staging region: [A][B] alternate for collectives, [C] point-to-point
     uint32_t epoch[dlbb::kPadBanks] = {0, 0, 0, 0};  // last epoch value used on each pad bank
     uint32_t send_epoch[DLBB_MAX_RANKS] = {};      // point-to-point: messages sent to / received from each peer

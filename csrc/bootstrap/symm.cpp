@@ -179,6 +179,8 @@ void fill_dev(dlbb_comm* c) {
             c->dev.pads[p] = reinterpret_cast<uint32_t*>(c->segs[c->pad_seg].va[p]);
     if (c->stage_seg >= 0)
         for (int p = 0; p < c->world; ++p) c->dev.stage[p] = reinterpret_cast<char*>(c->segs[c->stage_seg].va[p]);
+    for (int p = 0; p < DLBB_MAX_RANKS; ++p)
+        c->dev.tile_flags[p] = (c->flag_seg >= 0 && p < c->world) ? reinterpret_cast<uint32_t*>(c->segs[c->flag_seg].va[p]) : nullptr;
     c->dev.pads_mc = c->pad_seg >= 0 ? reinterpret_cast<uint32_t*>(c->segs[c->pad_seg].mc_va) : nullptr;
     c->dev.stage_mc = c->stage_seg >= 0 ? reinterpret_cast<char*>(c->segs[c->stage_seg].mc_va) : nullptr;
 }
@@ -344,6 +346,7 @@ int dlbb_comm_create(int rank, int world, int device, const char* job, size_t st
     c->stage_bytes = round_up(staging_bytes, 1 << 20);
     int rc = dlbb_symm_alloc(c, dlbb::kPadBytes, &c->pad_seg);
     if (rc == 0) rc = dlbb_symm_alloc(c, 3 * c->stage_bytes, &c->stage_seg);
+    if (rc == 0) rc = dlbb_symm_alloc(c, dlbb::kTileFlagBytes, &c->flag_seg);
     if (rc != 0) { delete c->bs; delete c; return rc; }
     fill_dev(c);
     const char* e = getenv("DLBB_CTAS");

@@ -218,8 +218,8 @@ class LLMEngine:
             if self.dense_qkv_backward:
                 a["dqkv"] = torch.zeros(tokens, 3 * H, dtype=bf, device=dev)
         else:
-            a["xa"] = buf(tokens, H)
-            a["xb"] = buf(tokens, H)
+            symm = self.allreduce.symm_buffers(tokens, H) if hasattr(self.allreduce, "symm_buffers") else None
+            a["xa"], a["xb"] = symm if symm is not None else (buf(tokens, H), buf(tokens, H))
             a["h"] = buf(tokens, H)
             a["qkv"] = buf(tokens, 3 * H // tp)
             a["act"] = buf(tokens, F // tp)

@@ -34,6 +34,7 @@ class _Reducer:
         self.device = device
         self.symm = None
         self.partial = None
+        self._symm_key, self._by_ptr, self._part, self._outs = None, {}, None, None
         if world_size == 1:
             return
         from ..parallel.symm import SymmComm
@@ -50,7 +51,24 @@ class _Reducer:
                 be.init_process_group(None, rank=rank, world_size=world_size)
             self.dist = dist
 
+    def symm_buffers(self, tokens: int, hidden: int):
+        """Activation buffers the fused GEMM + all-reduce kernel can write on every rank (symmetric
+        memory): two ping-pong outputs and the partial-sum matrix.  None when there is no NVLink transport."""
+        if self.symm is None or os.environ.get("DLBB_TP_FUSED", "1") != "1":
+            return None
+        key = (tokens, hidden)
+        if self._symm_key != key:
+            self._part = self.symm.alloc_matrix(tokens, hidden)
+            self._outs = [self.symm.alloc_matrix(tokens, hidden) for _ in range(2)]
+            self._by_ptr = {m.tensor.data_ptr(): m for m in self._outs}
+            self._symm_key = key
+        return self._outs[0].tensor, self._outs[1].tensor
+
     def __call__(self, inp: torch.Tensor, w: torch.Tensor, residual: torch.Tensor | None, out: torch.Tensor):
+        fused_out = self._by_ptr.get(out.data_ptr()) if self.symm is not None else None
+        if fused_out is not None:
+            # one kernel: tcgen05 GEMM, partial tiles reduced across ranks over NVLink while later tiles compute
+            return self.symm.gemm_allreduce(inp, w, self._part, fused_out, residual=residual)
         if self.partial is None or self.partial.shape != out.shape:
             self.partial = torch.empty_like(out)
         ops.matmul(inp, w, out=self.partial)

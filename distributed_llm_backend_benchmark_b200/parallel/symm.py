@@ -52,6 +52,7 @@ _SIGS = {
     "dlbb_alltoall": (I, [VP, VP, VP, I64, I, VP]),
     "dlbb_sendrecv": (I, [VP, VP, I64, I, VP, I64, I, I, VP]),
     "dlbb_fused_reduce_adam_bf16": (I, [VP, I, I, I64, I64, VP, VP, VP, F, F, F, F, F, F, I, I, VP]),
+    "dlbb_gemm_allreduce_bf16": (I, [VP, VP, VP, I, I, I, I64, I64, I, I, I, I64, I, I64, VP, I64, I, VP]),
 }
 _bound = False
 
@@ -248,6 +249,31 @@ class SymmComm:
     def recv(self, t: torch.Tensor, peer: int):
         return self.sendrecv(None, -1, t, peer)
 
+    # ------------------------------------------------------------------ fused GEMM + all-reduce (TP row-parallel)
+    def alloc_matrix(self, rows: int, cols: int) -> "SymmMatrix":
+        """Collective.  A bf16 [rows, cols] matrix in symmetric memory (peers can read / write it)."""
+        t, seg = self.alloc(rows * cols, torch.bfloat16)
+        return SymmMatrix(t.view(rows, cols), seg, 0)
+
+    def gemm_allreduce(self, a: torch.Tensor, b: torch.Tensor, part: "SymmMatrix", out: "SymmMatrix",
+                       residual: torch.Tensor | None = None, transpose_a: bool = False, transpose_b: bool = False,
+                       use_multicast: bool | None = None) -> torch.Tensor:
+        """out = all_reduce_sum(op(a) @ op(b)) + residual, one kernel (csrc/collectives/gemm_allreduce.cu)."""
+        M, K = (a.shape[1], a.shape[0]) if transpose_a else (a.shape[0], a.shape[1])
+        N = b.shape[0] if transpose_b else b.shape[1]
+        assert tuple(out.tensor.shape) == (M, N) and part.tensor.numel() >= M * N
+        assert a.stride(-1) == 1 and b.stride(-1) == 1 and a.dtype == torch.bfloat16
+        if use_multicast is None:
+            use_multicast = os.environ.get("DLBB_TP_MULTICAST", "1") == "1"
+        lda = a.stride(0) if a.shape[0] > 1 else a.shape[1]
+        ldb = b.stride(0) if b.shape[0] > 1 else b.shape[1]
+        _lib.check(self.lib.dlbb_gemm_allreduce_bf16(
+            self.h, a.data_ptr(), b.data_ptr(), M, N, K, lda, ldb, 1 if transpose_a else 0, 0 if transpose_b else 1,
+            part.seg, part.elem_off, out.seg, out.elem_off, residual.data_ptr() if residual is not None else None,
+            residual.stride(0) if residual is not None else 0, 1 if use_multicast else 0, _stream(self.device)),
+            "gemm_allreduce")
+        return out.tensor
+
     # ------------------------------------------------------------------ data-parallel fused step
     def alloc_dp_buffers(self, numel: int) -> tuple[torch.Tensor, torch.Tensor]:
         """Symmetric bf16 parameter and gradient buffers for the DP engine."""
@@ -276,3 +302,12 @@ class SymmComm:
 
     def dp_step_end(self) -> None:
         pass
+
+
+class SymmMatrix:
+    """A tensor living in a symmetric segment plus where it lives (segment id, element offset)."""
+
+    __slots__ = ("tensor", "seg", "elem_off")
+
+    def __init__(self, tensor: torch.Tensor, seg: int, elem_off: int):
+        self.tensor, self.seg, self.elem_off = tensor, seg, elem_off

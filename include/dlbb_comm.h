@@ -118,6 +118,20 @@ int dlbb_fused_reduce_adam_bf16(dlbb_comm_t* c, int grads_seg, int params_seg, i
                                 float beta2, float eps, float weight_decay, float grad_scale,
                                 int step, int use_multicast, void* stream);
 
+/* ------------------------------------------------------------------------------------------
+ * Fused row-parallel linear (K16): out = all_reduce_sum(A . B) + residual in ONE kernel - the tcgen05
+ * GEMM whose epilogue publishes partial tiles in symmetric memory while reducer warps of the same
+ * kernel sum finished tiles across ranks (multimem.ld_reduce or peer loads) and write the result to
+ * every rank (multimem.st or peer stores).  ref models.py:73-100 + :173/:188.
+ * A/B as in dlbb_gemm_bf16 (this rank's K-shard).  The partial buffer (M*N bf16) and the output
+ * buffer (M*N bf16, row-major, ld = N) live in symmetric segments at the given element offsets;
+ * residual (may be NULL) is a local [M, ld_res] bf16 matrix, identical on every rank.
+ */
+int dlbb_gemm_allreduce_bf16(dlbb_comm_t* c, const void* A, const void* B, int M, int N, int K,
+                             int64_t lda, int64_t ldb, int a_mn_major, int b_mn_major, int part_seg,
+                             int64_t part_elem_off, int out_seg, int64_t out_elem_off,
+                             const void* residual, int64_t ld_res, int use_multicast, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

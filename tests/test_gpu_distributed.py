@@ -160,3 +160,37 @@ print("DP_OK" if (err < 0.05 and same) else "DP_BAD", r, err, stats["losses"])
 """)
     r = run([BIN / "b200run", "-np", n, sys.executable, script], env={"MASTER_PORT": "29651"})
     assert r.returncode == 0 and r.stdout.count("DP_OK") == n, r.stdout[-3000:] + r.stderr[-3000:]
+
+
+def test_tp_forward_fused_gemm_allreduce_matches_unsharded(native_lib, tmp_path):
+    """Tensor-parallel forward (fused tcgen05 GEMM + NVLink all-reduce + residual in one kernel) against
+    the same model on a single rank with the full weights."""
+    n = nranks()
+    script = tmp_path / "tp.py"
+    script.write_text(f"""
+import sys, os; sys.path[:0] = [{str(ROOT)!r}, {str(ROOT / 'compat')!r}]
+import torch
+from mpi4py import MPI
+from distributed_llm_backend_benchmark_b200 import _lib
+from distributed_llm_backend_benchmark_b200.models import LLM, LLMConfig, LLMEngine
+comm = MPI.COMM_WORLD; r, w = comm.Get_rank(), comm.Get_size()
+torch.cuda.set_device(int(os.environ['LOCAL_RANK']))
+H, F, L = 1024, 2048, 3
+full = LLMEngine(LLMConfig(H, L, 8, F), torch.device('cuda', torch.cuda.current_device()), seed=7)
+for lv in full.layers:
+    for t in (lv.wqkv, lv.wo, lv.wup, lv.wdown): t.mul_(0.02)
+m = LLM(H, L, 8, F, r, w, comm)
+for lf, ls in zip(full.layers, m.engine.layers):
+    ls.wqkv.copy_(torch.cat([lf.wqkv[:, :H][:, r*H//w:(r+1)*H//w], lf.wqkv[:, H:][:, :3*H//w - H//w]], 1))
+    ls.wo.copy_(lf.wo[r*H//w:(r+1)*H//w]); ls.wup.copy_(lf.wup[:, r*F//w:(r+1)*F//w]); ls.wdown.copy_(lf.wdown[r*F//w:(r+1)*F//w])
+x = torch.randn(4, 200, H, generator=torch.Generator().manual_seed(1)).bfloat16().cuda()
+for rep in range(3):
+    y = m(x)
+yf = full(x)
+torch.cuda.synchronize()
+err = ((y.float() - yf.float()).norm() / yf.float().norm()).item()
+fused = w > 1 and m.engine._act['xa'].data_ptr() in m._reduce._by_ptr
+print('TP_OK' if err < 3e-2 and (fused or w == 1) else 'TP_BAD', r, err, fused)
+""")
+    r = run([BIN / "mpirun", "-np", n, sys.executable, script])
+    assert r.returncode == 0 and r.stdout.count("TP_OK") == n, r.stdout[-3000:] + r.stderr[-3000:]

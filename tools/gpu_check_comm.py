@@ -113,6 +113,28 @@ try:
     del xs, x, out
     torch.cuda.synchronize()
 
+    # fused GEMM + all-reduce + residual (row-parallel linear in one kernel)
+    for (M, N, Kt) in ((512, 1024, 256 * world), (200, 136, 64 * world), (4096, 4096, 512 * world)):
+        Kr = Kt // world
+        def mk(r, rows, cols, seed, scale=1.0):
+            g = torch.Generator(device=dev); g.manual_seed(7000 + 31 * seed + r)
+            return (torch.randn(rows, cols, device=dev, generator=g) * scale).bfloat16()
+        As = [mk(r, M, Kr, 1) for r in range(world)]; Bs = [mk(r, Kr, N, 2, 0.2) for r in range(world)]
+        resid_t = mk(0, M, N, 3, 4.0)
+        part, out = comm.alloc_matrix(M, N), comm.alloc_matrix(M, N)
+        ref = sum(ops.matmul(a, b).float() for a, b in zip(As, Bs)) + resid_t.float()   # bf16 partials, like the kernel
+        for use_mc in ([False, True] if comm.has_multicast else [False]):
+            for rep in range(2):
+                out.tensor.fill_(7.0); torch.cuda.synchronize(); comm.host_barrier()
+                comm.gemm_allreduce(As[rank], Bs[rank], part, out, residual=resid_t, use_multicast=use_mc)
+                torch.cuda.synchronize(); comm.host_barrier()
+            check(f"gemm_allreduce_{M}x{N}x{Kt}_mc{int(use_mc)}", out.tensor, ref.bfloat16(), 3e-2)
+        # transposed B (weights stored [out, in]) and no residual
+        Bt = [b.t().contiguous() for b in Bs]
+        comm.gemm_allreduce(As[rank], Bt[rank], part, out, transpose_b=True, use_multicast=False)
+        torch.cuda.synchronize(); comm.host_barrier()
+        check(f"gemm_allreduce_tb_{M}x{N}x{Kt}", out.tensor, (ref - resid_t.float()).bfloat16(), 3e-2)
+
     # fused reduce + Adam + broadcast
     for use_mc in ([False, True] if comm.has_multicast else [False]):
         n = 3 * 8 * world * 1000 + 8 * 5 + 3   # ragged on purpose
@@ -182,6 +204,31 @@ if ok_all and os.environ.get("DLBB_SKIP_PERF") != "1":
             if rank == 0: P("PERF", json.dumps({k: (round(v, 1) if isinstance(v, float) else v) for k, v in row.items()}))
     except Exception as e:
         import traceback; traceback.print_exc(); res["perf_exception"] = repr(e)
+
+if ok_all and os.environ.get("DLBB_SKIP_PERF") != "1":
+    try:
+        # 7B out-projection / FFN-down shapes under tensor parallelism: fused kernel vs GEMM followed by all-reduce
+        for name, M, N, Kt in (("out_proj", 4096, 4096, 4096), ("ffn_down", 4096, 4096, 16384)):
+            Kr = Kt // world
+            A = torch.randn(M, Kr, device=dev).bfloat16(); B = (torch.randn(Kr, N, device=dev) * 0.1).bfloat16()
+            resid = torch.randn(M, N, device=dev).bfloat16()
+            part, out = comm.alloc_matrix(M, N), comm.alloc_matrix(M, N)
+            tmp = torch.empty(M, N, device=dev, dtype=torch.bfloat16); o2 = torch.empty_like(tmp)
+            row = {"shape": name, "M": M, "N": N, "K_total": Kt}
+            row["gemm_only_us"] = timeit(lambda: ops.matmul(A, B, out=tmp), 20) * 1e3
+            row["unfused_ours_us"] = timeit(lambda: (ops.matmul(A, B, out=tmp), comm.all_reduce_residual(tmp, resid, o2)), 20) * 1e3
+            def nccl_path():
+                torch.matmul(A, B, out=tmp); dist.all_reduce(tmp); torch.add(tmp, resid, out=o2)
+            row["cublas_nccl_us"] = timeit(nccl_path, 20) * 1e3
+            row["fused_p2p_us"] = timeit(lambda: comm.gemm_allreduce(A, B, part, out, residual=resid, use_multicast=False), 20) * 1e3
+            if comm.has_multicast:
+                row["fused_nvls_us"] = timeit(lambda: comm.gemm_allreduce(A, B, part, out, residual=resid, use_multicast=True), 20) * 1e3
+            flops = 2.0 * M * N * Kr; wire = 2.0 * (world - 1) / world * M * N * 2
+            row["roofline_us"] = max(flops / 1.4118e15, wire / 770e9) * 1e6
+            res["perf"].append(row)
+            if rank == 0: P("FUSED", json.dumps({k: (round(v, 1) if isinstance(v, float) else v) for k, v in row.items()}))
+    except Exception as e:
+        import traceback; traceback.print_exc(); res["fused_perf_exception"] = repr(e)
 
 res["ok"] = bool(ok_all)
 flag = torch.tensor([1 if ok_all else 0], device=dev); dist.all_reduce(flag, op=dist.ReduceOp.MIN)
