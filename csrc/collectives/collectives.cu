@@ -550,8 +550,12 @@ static int allreduce_impl(dlbb_comm* c, const void* in, void* out, const void* e
     if (algo == DLBB_ALGO_AUTO) algo = c->default_algo;
     const int64_t VE = 16 / (int64_t)es;
     const int64_t cap = static_cast<int64_t>(c->stage_bytes / es) / (VE * c->world) * (VE * c->world);
-    const int64_t oneshot_max = c->oneshot_max ? (int64_t)c->oneshot_max : (c->world <= 2 ? (4 << 20) : (512 << 10));
     const bool nvls_ok = dlbb_comm_has_multicast(c) && op == DLBB_SUM && (dtype == DLBB_F16 || dtype == DLBB_BF16 || dtype == DLBB_F32);
+    // Measured crossovers (profiles/collectives_busbw.md).  Two ranks: one-shot moves the minimum number of bytes
+    // (each rank reads the peer once) and wins at every size.  More ranks with NVLS: the multimem kernel wins from
+    // 1 KiB (14 us) to 1 GiB.  Without multicast: one-shot up to 512 KiB, then two-shot.
+    int64_t oneshot_max = c->oneshot_max ? (int64_t)c->oneshot_max
+                        : (c->world <= 2 ? INT64_MAX : (nvls_ok && algo == DLBB_ALGO_AUTO ? 0 : (512 << 10)));
     int64_t done = 0;
     while (done < count) {
         const int64_t left = count - done;
