@@ -239,6 +239,10 @@ def _apply_env(spec: SweepSpec, three_d: bool) -> SweepSpec:
     spec.warmup = int(os.environ.get("DLBB_SWEEP_WARMUP", spec.warmup))
     spec.operations = _env_list("DLBB_SWEEP_OPS", spec.operations)
     spec.output_dir = os.environ.get("DLBB_OUTPUT_DIR", spec.output_dir)
+    if os.environ.get("DLBB_SWEEP_BACKEND") and spec.flavour == "deepspeed":
+        # baseline arm: the same loops on another torch.distributed backend (e.g. nccl), SURVEY.md 6.4
+        spec.backend = os.environ["DLBB_SWEEP_BACKEND"]
+        spec.implementation = f"deepspeed_{spec.backend}"
     if not three_d and os.environ.get("DLBB_SWEEP_SIZES"):
         chosen = {}
         for tok in _env_list("DLBB_SWEEP_SIZES", []):
@@ -279,6 +283,9 @@ class _World:
             self.rank, self.world = dist.get_rank(), dist.get_world_size()
             if spec.backend == "gloo":
                 self.device = torch.device("cpu")
+            # bookkeeping collectives (timing gather, skip votes) use host tensors, except on backends
+            # that only serve CUDA tensors (nccl)
+            self.helper_device = self.device if spec.backend == "nccl" else torch.device("cpu")
             self.transport = TorchTransport(dist, self.rank, self.world, self.device)
 
     def gather_timings(self, values):
@@ -287,7 +294,7 @@ class _World:
             return None
         if self.spec.flavour == "mpi":
             return self.comm.gather(list(values), root=0)
-        t = torch.tensor(values, dtype=torch.float64)
+        t = torch.tensor(values, dtype=torch.float64, device=self.helper_device)
         if self.world == 1:
             return [t.tolist()]
         bucket = [torch.zeros_like(t) for _ in range(self.world)] if self.rank == 0 else None
@@ -300,7 +307,7 @@ class _World:
             return mine
         if self.spec.flavour == "mpi":
             return bool(self.comm.allreduce(1 if mine else 0, op=self.MPI.MAX))
-        flag = torch.tensor([1.0 if mine else 0.0])
+        flag = torch.tensor([1.0 if mine else 0.0], device=self.helper_device)
         self.dist.all_reduce(flag, op=self.dist.ReduceOp.MAX)
         return bool(flag.item() > 0)
 
