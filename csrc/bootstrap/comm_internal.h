@@ -17,7 +17,8 @@ constexpr int kPadStride = DLBB_MAX_RANKS;  // uint32 slots per row
 // a second bank of the same shape for the fused DP kernel (it runs on a side stream concurrently
 // with collectives issued on the main stream, so it must not share rows or epochs with them).
 constexpr int kPadWordsPerBank = kMaxCtas * kPadStride;
-constexpr int kPadBanks = 4;          // 0: collectives, 1: fused DP kernel, 2: fused GEMM+all-reduce, 3: point-to-point
+constexpr int kPadBanks = 6;          // 0: collectives, 1: fused DP kernel, 2: fused GEMM+all-reduce, 3: point-to-point,
+                                      // 4/5: pack-done / reduce-done flags of the pipelined all-reduce
 constexpr size_t kPadBytes = sizeof(uint32_t) * kPadWordsPerBank * kPadBanks;
 // Per-tile arrival flags of the fused GEMM + all-reduce: [tile][source rank], epoch valued.
 constexpr size_t kMaxFusedTiles = 16384;
@@ -53,7 +54,7 @@ struct dlbb_comm {
     size_t gran = 2u << 20;
     int pad_seg = -1, stage_seg = -1, flag_seg = -1;
     size_t stage_bytes = 0;        // bytes of each staging region: [A][B] alternate for collectives, [C] point-to-point
-    uint32_t epoch[dlbb::kPadBanks] = {0, 0, 0, 0};  // last epoch value used on each pad bank
+    uint32_t epoch[dlbb::kPadBanks] = {0, 0, 0, 0, 0, 0};  // last epoch value used on each pad bank
     uint32_t send_epoch[DLBB_MAX_RANKS] = {};      // point-to-point: messages sent to / received from each peer
     uint32_t recv_epoch[DLBB_MAX_RANKS] = {};
     unsigned parity = 0;           // alternates the staging half used by single-barrier kernels

@@ -341,7 +341,7 @@ int dlbb_comm_create(int rank, int world, int device, const char* job, size_t st
     }
     if (staging_bytes == 0) {
         const char* e = getenv("DLBB_STAGING_MB");
-        staging_bytes = (e ? static_cast<size_t>(atol(e)) : 64) << 20;
+        staging_bytes = (e ? static_cast<size_t>(atol(e)) : 256) << 20;   // fewer, longer launches for large messages
     }
     c->stage_bytes = round_up(staging_bytes, 1 << 20);
     int rc = dlbb_symm_alloc(c, dlbb::kPadBytes, &c->pad_seg);

@@ -14,6 +14,10 @@ namespace dlbb {
 #define DLBB_WATCHDOG 1
 #endif
 
+__device__ __forceinline__ void group_bar_sync(uint32_t id, uint32_t nthreads) {   // named barrier of a warp group
+    asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+
 // ------------------------------------------------------------------ flags
 __device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
     asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");

@@ -33,8 +33,8 @@ enum { DLBB_ALGO_AUTO = 0, DLBB_ALGO_ONESHOT = 1, DLBB_ALGO_TWOSHOT = 2, DLBB_AL
 
 /* Create a communicator.  `job` names the rendezvous (all ranks pass the same string, e.g.
  * "<MASTER_PORT>-<sequence>"); `device` is the CUDA ordinal this rank drives.  Collective call:
- * every rank must call it.  staging_bytes: size of each of the two staging regions (0 = default
- * 64 MiB, or DLBB_STAGING_MB). */
+ * every rank must call it.  staging_bytes: size of each of the three staging regions (0 = default
+ * 256 MiB, or DLBB_STAGING_MB). */
 int dlbb_comm_create(int rank, int world, int device, const char* job, size_t staging_bytes,
                      dlbb_comm_t** out);
 int dlbb_comm_destroy(dlbb_comm_t* c);
