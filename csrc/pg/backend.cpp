@@ -162,6 +162,29 @@ class BackendDlbb : public c10d::Backend {
         return finish(c10d::OpType::ALLREDUCE, s, {t});
     }
 
+    // Bucket fusion (the analogue of CCL_FUSION, collectives/3d/launch_dsccl.sh:49-59): many small tensors
+    // travel as one flat bucket -> one collective kernel instead of one per tensor.
+    c10::intrusive_ptr<Work> allreduce_coalesced(std::vector<at::Tensor>& tensors,
+                                                 const c10d::AllreduceCoalescedOptions& opts) override {
+        TORCH_CHECK(!tensors.empty(), "dlbb backend: empty tensor list");
+        std::vector<at::Tensor> flat_parts;
+        flat_parts.reserve(tensors.size());
+        c10::cuda::CUDAGuard g(dev_);
+        for (auto& t : tensors) flat_parts.push_back(t.to(c10::Device(c10::kCUDA, dev_)).reshape({-1}));
+        at::Tensor bucket = at::cat(flat_parts);
+        DLBB_CALL(dlbb_allreduce(comm_, bucket.data_ptr(), bucket.data_ptr(), bucket.numel(),
+                                 to_dlbb_dtype(bucket.scalar_type(), true), to_dlbb_op(opts.reduceOp), algo_, nullptr, stream()));
+        if (opts.reduceOp == c10d::ReduceOp::AVG) bucket.div_(getSize());
+        int64_t off = 0;
+        bool any_cpu = false;
+        for (auto& t : tensors) {
+            t.copy_(bucket.narrow(0, off, t.numel()).view_as(t));
+            off += t.numel();
+            any_cpu = any_cpu || !t.is_cuda();
+        }
+        return done(c10d::OpType::ALLREDUCE_COALESCED, tensors, !any_cpu);
+    }
+
     c10::intrusive_ptr<Work> broadcast(std::vector<at::Tensor>& tensors, const c10d::BroadcastOptions& opts) override {
         TORCH_CHECK(tensors.size() == 1, "dlbb backend: one tensor per rank");
         at::Tensor& t = tensors[0];

@@ -16,6 +16,7 @@ from __future__ import annotations
 import torch
 
 from .. import ops
+from ..utils.trace import nvtx_range
 from ..models.llm import LLMEngine
 
 
@@ -123,7 +124,8 @@ class DataParallelTrainer:
         eng = self.engine
         if self.comm is not None and self.world > 1:
             self.comm.dp_step_begin()
-        loss = eng.forward_backward(x, target, on_bucket_ready=self._on_bucket_ready if self.overlap else None)
+        with nvtx_range(f"dp_step_{self.step_count}"):
+            loss = eng.forward_backward(x, target, on_bucket_ready=self._on_bucket_ready if self.overlap else None)
         if self.overlap:
             self.done.record(self.side)
             torch.cuda.current_stream(eng.device).wait_event(self.done)

@@ -81,6 +81,23 @@ class Trainer:
                 "h2d_bytes_per_step": self.feeder.bytes_per_step, "d2h_bytes_per_step": 4,
                 "samples_per_step": self.batch_size * self.world}
 
+    # ------------------------------------------------------------------ checkpoint / resume
+    def save_checkpoint(self, path: str) -> None:
+        """Every rank writes its own file (`<path>.rank<r>`): the optimizer state is sharded over the ranks."""
+        if self.backend != "native":
+            raise NotImplementedError("checkpointing is implemented for the native backend")
+        sd = self.dp.state_dict()
+        torch.save({k: (v.cpu() if isinstance(v, torch.Tensor) else v) for k, v in sd.items()}
+                   | {"world_size": self.world, "config": self.config}, f"{path}.rank{self.rank}")
+
+    def load_checkpoint(self, path: str) -> None:
+        sd = torch.load(f"{path}.rank{self.rank}", map_location=self.device, weights_only=False)
+        if sd.get("world_size") != self.world:
+            raise ValueError(f"checkpoint was written by {sd.get('world_size')} ranks, this job has {self.world}")
+        self.dp.load_state_dict(sd)
+        if self.comm is not None:
+            self.comm.barrier()
+
     def flops_per_step(self) -> float:
         """FLOPs actually executed per rank per step (forward + backward without the structurally
         zero 2/3 of the QKV backward, unless DLBB_DENSE_QKV_BWD=1)."""

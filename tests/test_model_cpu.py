@@ -117,3 +117,18 @@ def test_trainer_reduces_loss_and_matches_torch_adam():
     assert moved[~nz].abs().max() == 0
     losses = [l0] + [tr.step(x, t).item() for _ in range(5)]
     assert losses[-1] < losses[0]
+
+
+def test_trainer_checkpoint_roundtrip(tmp_path):
+    from distributed_llm_backend_benchmark_b200.train import Trainer
+    cfg = {"experiment": {"name": "t", "output_dir": str(tmp_path)},
+           "model": {"size": "t", "hidden_size": 64, "num_layers": 2, "num_heads": 4, "ffn_intermediate": 128},
+           "parallelism": {"world_size": 1, "cores_per_rank": 1}, "input": {"batch_size": 2, "sequence_length": 8, "seed": 3},
+           "execution": {"warmup_iterations": 1, "benchmark_iterations": 1}, "system": {}}
+    a = Trainer(cfg, device="cpu", rank=0, world_size=1, lr=1e-3)
+    a.fit(steps=2)
+    a.save_checkpoint(str(tmp_path / "ck"))
+    b = Trainer(cfg, device="cpu", rank=0, world_size=1, lr=1e-3, seed=999)    # different init
+    b.load_checkpoint(str(tmp_path / "ck"))
+    la, lb = a.fit(steps=2)["losses"], b.fit(steps=2)["losses"]
+    assert la == lb and b.dp.step_count == 4

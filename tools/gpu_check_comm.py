@@ -13,7 +13,7 @@ rank, world, lr = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os
 torch.cuda.set_device(lr)
 dev = torch.device("cuda", lr)
 dist.init_process_group("nccl", device_id=dev)
-comm = SymmComm.from_env(dev)
+comm = SymmComm.from_env(dev, staging_mb=64)     # small staging: the 80 MB cases below exercise the chunked paths
 res = {"world": world, "multicast": comm.has_multicast, "checks": {}, "perf": []}
 ok_all = True
 P = lambda *a: print(f"[r{rank}]", *a, flush=True)
@@ -182,6 +182,9 @@ def timeit(fn, iters, warm=3):
     dist.all_reduce(t, op=dist.ReduceOp.MAX)
     return t.item()
 
+if ok_all and os.environ.get("DLBB_SKIP_PERF") != "1":
+    comm.destroy()
+    comm = SymmComm.from_env(dev)                    # default staging for the bandwidth tables
 if ok_all and os.environ.get("DLBB_SKIP_PERF") != "1":
     try:
         for nbytes in (1 << 10, 1 << 13, 1 << 16, 1 << 19, 1 << 22, 1 << 25, 1 << 27, 1 << 30):
