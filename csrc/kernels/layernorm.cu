@@ -123,18 +123,34 @@ ln_bwd_vec_kernel(const uint4* __restrict__ dy, const uint4* __restrict__ x,
 #pragma unroll
         for (int j = 0; j < 8; ++j) { pg[i][j] = 0.f; pb[i][j] = 0.f; }
     }
+    // Software pipeline over this CTA's rows: the loads of row r+1 are issued before the two block-wide
+    // reductions of row r, so HBM latency hides behind the barriers instead of adding to them.
+    uint4 nd[VPT], nx[VPT], nr[VPT];
+    auto fetch = [&](int row) {
+#pragma unroll
+        for (int i = 0; i < VPT; ++i) {
+            const int c = threadIdx.x + i * kLnThreads;
+            if (c < nvec) {
+                nd[i] = dy[(size_t)row * nvec + c];
+                nx[i] = x[(size_t)row * nvec + c];
+                if (dres) nr[i] = dres[(size_t)row * nvec + c];
+            }
+        }
+    };
+    if ((int)blockIdx.x < rows) fetch(blockIdx.x);
     for (int row = blockIdx.x; row < rows; row += gridDim.x) {
         const float mu = mean[row], rs = rstd[row];
-        const uint4* dyr = dy + (size_t)row * nvec;
-        const uint4* xr = x + (size_t)row * nvec;
+        uint4 cd[VPT], cx[VPT], cr[VPT];
+#pragma unroll
+        for (int i = 0; i < VPT; ++i) { cd[i] = nd[i]; cx[i] = nx[i]; cr[i] = nr[i]; }
+        if (row + (int)gridDim.x < rows) fetch(row + gridDim.x);
         float xh[VPT][8], g[VPT][8];
         float s1 = 0.f, s2 = 0.f;
 #pragma unroll
         for (int i = 0; i < VPT; ++i) {
             const int c = threadIdx.x + i * kLnThreads;
             if (c < nvec) {
-                const uint4 ud = dyr[c], ux = xr[c];
-                const uint32_t dw[4] = {ud.x, ud.y, ud.z, ud.w}, xw[4] = {ux.x, ux.y, ux.z, ux.w};
+                const uint32_t dw[4] = {cd[i].x, cd[i].y, cd[i].z, cd[i].w}, xw[4] = {cx[i].x, cx[i].y, cx[i].z, cx[i].w};
 #pragma unroll
                 for (int j = 0; j < 4; ++j) {
                     const float2 d = unpack_bf16x2(dw[j]), xx = unpack_bf16x2(xw[j]);
@@ -163,8 +179,7 @@ ln_bwd_vec_kernel(const uint4* __restrict__ dy, const uint4* __restrict__ x,
 #pragma unroll
                 for (int j = 0; j < 8; ++j) r[j] = rs * (g[i][j] - c1 - xh[i][j] * c2);
                 if (dres) {
-                    const uint4 ur = dres[(size_t)row * nvec + c];
-                    const uint32_t rw[4] = {ur.x, ur.y, ur.z, ur.w};
+                    const uint32_t rw[4] = {cr[i].x, cr[i].y, cr[i].z, cr[i].w};
 #pragma unroll
                     for (int j = 0; j < 4; ++j) {
                         const float2 f = unpack_bf16x2(rw[j]);
@@ -290,7 +305,7 @@ static int ln_bwd_parts(int rows) {
             cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess)
             sms = 148;
     }
-    return rows < 4 * sms ? rows : 4 * sms;
+    return rows < 2 * sms ? rows : 2 * sms;
 }
 
 }  // namespace dlbb

@@ -23,10 +23,8 @@ adam_bf16_kernel(__nv_bfloat16* __restrict__ param, const __nv_bfloat16* __restr
     int64_t done = 0;
     if (vec_ok) {
         const int64_t nvec = n >> 3;
-        const uint64_t pol = l2_policy_evict_first();   // 28 B/parameter of read-once / write-once traffic
-#pragma unroll 2
         for (int64_t i = tid; i < nvec; i += nthreads) {
-            const uint4 ug = ld_u4_stream(reinterpret_cast<const uint4*>(grad) + i, pol);
+            const uint4 ug = reinterpret_cast<const uint4*>(grad)[i];
             const uint32_t gw[4] = {ug.x, ug.y, ug.z, ug.w};
             float g[8], w[8], mm[8], vv[8];
 #pragma unroll
@@ -36,19 +34,19 @@ adam_bf16_kernel(__nv_bfloat16* __restrict__ param, const __nv_bfloat16* __restr
             }
             float4* m4 = reinterpret_cast<float4*>(m) + 2 * i;
             float4* v4 = reinterpret_cast<float4*>(v) + 2 * i;
-            const float4 ma = ld_f4_stream(m4, pol), mb = ld_f4_stream(m4 + 1, pol);
-            const float4 va = ld_f4_stream(v4, pol), vb = ld_f4_stream(v4 + 1, pol);
+            const float4 ma = m4[0], mb = m4[1];
+            const float4 va = v4[0], vb = v4[1];
             mm[0] = ma.x; mm[1] = ma.y; mm[2] = ma.z; mm[3] = ma.w;
             mm[4] = mb.x; mm[5] = mb.y; mm[6] = mb.z; mm[7] = mb.w;
             vv[0] = va.x; vv[1] = va.y; vv[2] = va.z; vv[3] = va.w;
             vv[4] = vb.x; vv[5] = vb.y; vv[6] = vb.z; vv[7] = vb.w;
             if (master) {
-                const float4 wa = ld_f4_stream(reinterpret_cast<const float4*>(master) + 2 * i, pol);
-                const float4 wb = ld_f4_stream(reinterpret_cast<const float4*>(master) + 2 * i + 1, pol);
+                const float4 wa = reinterpret_cast<const float4*>(master)[2 * i];
+                const float4 wb = reinterpret_cast<const float4*>(master)[2 * i + 1];
                 w[0] = wa.x; w[1] = wa.y; w[2] = wa.z; w[3] = wa.w;
                 w[4] = wb.x; w[5] = wb.y; w[6] = wb.z; w[7] = wb.w;
             } else {
-                const uint4 up = ld_u4_stream(reinterpret_cast<const uint4*>(param) + i, pol);
+                const uint4 up = reinterpret_cast<const uint4*>(param)[i];
                 const uint32_t pw[4] = {up.x, up.y, up.z, up.w};
 #pragma unroll
                 for (int j = 0; j < 4; ++j) {
@@ -58,17 +56,17 @@ adam_bf16_kernel(__nv_bfloat16* __restrict__ param, const __nv_bfloat16* __restr
             }
 #pragma unroll
             for (int j = 0; j < 8; ++j) adam_update(w[j], mm[j], vv[j], g[j], h);
-            st_f4_stream(m4, make_float4(mm[0], mm[1], mm[2], mm[3]), pol);
-            st_f4_stream(m4 + 1, make_float4(mm[4], mm[5], mm[6], mm[7]), pol);
-            st_f4_stream(v4, make_float4(vv[0], vv[1], vv[2], vv[3]), pol);
-            st_f4_stream(v4 + 1, make_float4(vv[4], vv[5], vv[6], vv[7]), pol);
+            m4[0] = make_float4(mm[0], mm[1], mm[2], mm[3]);
+            m4[1] = make_float4(mm[4], mm[5], mm[6], mm[7]);
+            v4[0] = make_float4(vv[0], vv[1], vv[2], vv[3]);
+            v4[1] = make_float4(vv[4], vv[5], vv[6], vv[7]);
             if (master) {
-                st_f4_stream(reinterpret_cast<float4*>(master) + 2 * i, make_float4(w[0], w[1], w[2], w[3]), pol);
-                st_f4_stream(reinterpret_cast<float4*>(master) + 2 * i + 1, make_float4(w[4], w[5], w[6], w[7]), pol);
+                reinterpret_cast<float4*>(master)[2 * i] = make_float4(w[0], w[1], w[2], w[3]);
+                reinterpret_cast<float4*>(master)[2 * i + 1] = make_float4(w[4], w[5], w[6], w[7]);
             }
-            st_u4_stream(reinterpret_cast<uint4*>(param) + i,
-                         make_uint4(pack_bf16x2(w[0], w[1]), pack_bf16x2(w[2], w[3]), pack_bf16x2(w[4], w[5]),
-                                    pack_bf16x2(w[6], w[7])), pol);
+            reinterpret_cast<uint4*>(param)[i] =
+                make_uint4(pack_bf16x2(w[0], w[1]), pack_bf16x2(w[2], w[3]), pack_bf16x2(w[4], w[5]),
+                           pack_bf16x2(w[6], w[7]));
         }
         done = nvec << 3;
     }
