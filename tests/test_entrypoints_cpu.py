@@ -139,3 +139,11 @@ def test_sweeps_and_stats(tmp_path):
     assert res["tensor_shape"] == {"batch": 1, "seq_len": 16, "hidden_dim": 64} and res["tensor_size_bytes"] == 2048
     r = run([sys.executable, "stats.py", "dsgloo", tmp_path / "r3", tmp_path / "s3"], cwd=ROOT / "collectives" / "3d")
     assert r.returncode == 0 and (tmp_path / "s3" / "benchmark_statistics_3d_dsgloo_transpose.csv").exists()
+
+
+def test_mixed_collective_stress_two_ranks(tmp_path):
+    r = run([BIN / "deepspeed", "--master_port", 29573, "--include", "localhost:0,1", "stress.py"], cwd=ROOT / "collectives",
+            env={"DLBB_STRESS_ROUNDS": "4", "DLBB_OUTPUT_DIR": str(tmp_path)})
+    assert r.returncode == 0, r.stdout[-1500:] + r.stderr[-1500:]
+    res = json.loads((tmp_path / "stress_ccl_ranks2.json").read_text())
+    assert res["errors"] == 0 and res["num_ranks"] == 2 and len(res["alltoall"]) >= 4

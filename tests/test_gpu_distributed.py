@@ -194,3 +194,13 @@ print('TP_OK' if err < 3e-2 and (fused or w == 1) else 'TP_BAD', r, err, fused)
 """)
     r = run([BIN / "mpirun", "-np", n, sys.executable, script])
     assert r.returncode == 0 and r.stdout.count("TP_OK") == n, r.stdout[-3000:] + r.stderr[-3000:]
+
+
+def test_mixed_collective_stress_native(native_lib, tmp_path):
+    n = nranks()
+    inc = ",".join(str(i) for i in range(n))
+    r = run([BIN / "deepspeed", "--master_port", 29661, "--include", f"localhost:{inc}", "stress.py"], cwd=ROOT / "collectives",
+            env={"DLBB_STRESS_ROUNDS": "60", "DLBB_OUTPUT_DIR": str(tmp_path)})
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    res = json.loads((tmp_path / f"stress_ccl_ranks{n}.json").read_text())
+    assert res["errors"] == 0 and res["device"].startswith("cuda")
