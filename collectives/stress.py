@@ -43,6 +43,8 @@ def main():
     helper = dev if BACKEND == "nccl" else torch.device("cpu")
     rng = random.Random(1234)                      # same stream of choices on every rank
     ops = ["alltoall", "allreduce", "allgather", "reducescatter", "broadcast"] + (["sendrecv"] if world > 1 else [])
+    if os.environ.get("DLBB_STRESS_OPS"):       # e.g. the NCCL arm: unbatched isend/irecv rings can deadlock there
+        ops = [o for o in ops if o in os.environ["DLBB_STRESS_OPS"].split(",")]
     errors = 0
     t0 = time.perf_counter()
     for rnd in range(ROUNDS):
