@@ -163,6 +163,7 @@ def main() -> None:
 
     # ---------------- device-timed loop: batch resident, no host sync inside
     x_dev, t_dev = trainer.resident_batch()
+    barrier()
     for _ in range(args.warmup):
         trainer.step(x_dev, t_dev)
     barrier()

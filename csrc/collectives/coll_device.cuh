@@ -29,7 +29,7 @@ __device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
 }
 
 // Wait until *flag has reached `epoch` (monotonic, wrap-safe).  A peer that never arrives traps
-// after ~20 s instead of hanging the GPU (watchdog on device-side flag waits).
+// after ~60 s instead of hanging the GPU (watchdog on device-side flag waits).
 __device__ __forceinline__ void wait_flag(const uint32_t* flag, uint32_t epoch, int peer) {
 #if DLBB_WATCHDOG
     long long t0 = 0;
@@ -41,8 +41,8 @@ __device__ __forceinline__ void wait_flag(const uint32_t* flag, uint32_t epoch, 
             long long now;
             asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
             if (t0 == 0) t0 = now;
-            else if (now - t0 > 20000000000ll) {
-                printf("dlbb: device barrier timeout: block %d waited 20 s for rank %d (epoch %u, flag %u)\n",
+            else if (now - t0 > 60000000000ll) {
+                printf("dlbb: device barrier timeout: block %d waited 60 s for rank %d (epoch %u, flag %u)\n",
                        blockIdx.x, peer, epoch, *flag);
                 __trap();
             }

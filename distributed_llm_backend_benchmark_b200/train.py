@@ -44,6 +44,12 @@ class Trainer:
                                     grad_buffer=gbuf)
             self.dp = DataParallelTrainer(self.engine, lr=lr, comm=comm, overlap=overlap)
             self._step = self.dp.step
+            if comm is not None:
+                # Ranks finish weight initialisation at different times (a cold page cache can cost one of them
+                # tens of seconds); meet on the host so that the first device-side flag wait starts with every
+                # rank present - those waits have a watchdog.
+                torch.cuda.synchronize(self.device)
+                comm.host_barrier()
         elif backend == "torch-nccl":
             import importlib.util
             import pathlib
