@@ -23,11 +23,13 @@ constexpr int kEpiBufBytes = kBM * kEpiCols * 2;  // 8 KiB
 constexpr int kNumThreads = 256;
 constexpr int kEpiThreads = 128;
 
-template <int BN>
+// CG = CTAs per MMA (1, or 2 = a CTA pair sharing one 256 x BN tile; each CTA then stages only half of B).
+template <int BN, int CG = 1>
 struct GemmCfg {
-    static constexpr int kStages = (BN == 256) ? 4 : 6;
+    static constexpr int kBRows = BN / CG;   // B rows (N extent) staged by one CTA
+    static constexpr int kStages = (kBRows == 256) ? 4 : 6;
     static constexpr int kABytes = kBM * kBK * 2;
-    static constexpr int kBBytes = BN * kBK * 2;
+    static constexpr int kBBytes = kBRows * kBK * 2;
     static constexpr int kStageBytes = kABytes + kBBytes;
     static constexpr int kTileBytes = kStages * kStageBytes;
     static constexpr int kEpiBytes = 4 * kEpiBufBytes;  // out[2] + aux[2]
@@ -66,10 +68,11 @@ struct NoFusion {
     __device__ __forceinline__ void finish() {}
 };
 
-template <int BN, bool A_MN, bool B_MN, class Fusion>
+template <int BN, bool A_MN, bool B_MN, class Fusion, int CG = 1>
 __device__ __forceinline__ void gemm_cta_body(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC,
                                               const CUtensorMap& tmAux, const GemmParams& p, Fusion& fusion) {
-    using Cfg = GemmCfg<BN>;
+    using Cfg = GemmCfg<BN, CG>;
+    static_assert(CG == 1 || (CG == 2 && Fusion::kExtraWarps == 0), "pairs: plain GEMM only");
     extern __shared__ uint8_t smem_raw[];
     // 128B-swizzled operand tiles need 1024 B alignment.
     uint8_t* smem = reinterpret_cast<uint8_t*>(
@@ -87,7 +90,11 @@ __device__ __forceinline__ void gemm_cta_body(const CUtensorMap& tmA, const CUte
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
 
-    const int num_m = (p.M + kBM - 1) / kBM;
+    // CTA pair: rank within the pair, pair index and pair count replace block index and grid size.
+    const int cta_rank = (CG == 2) ? static_cast<int>(cluster_ctarank()) : 0;
+    const int worker = blockIdx.x / CG, num_workers = gridDim.x / CG;
+    constexpr int kTileM = kBM * CG;
+    const int num_m = (p.M + kTileM - 1) / kTileM;
     const int num_n = (p.N + BN - 1) / BN;
     const int num_tiles = num_m * num_n;
     const int num_k = (p.K + kBK - 1) / kBK;
@@ -104,48 +111,59 @@ __device__ __forceinline__ void gemm_cta_body(const CUtensorMap& tmA, const CUte
         }
         for (int s = 0; s < 2; ++s) {
             mbar_init(bar_tfull + 8 * s, 1);
-            mbar_init(bar_tempty + 8 * s, kEpiThreads);
+            mbar_init(bar_tempty + 8 * s, kEpiThreads * CG);
             mbar_init(bar_aux + 8 * s, 1);
         }
         fence_mbar_init();
     } else if (warp == 2) {
-        tmem_alloc(smem_u32(tmem_ptr_smem), Cfg::kTmemCols);
-        tmem_relinquish();
+        if constexpr (CG == 2) {
+            tmem_alloc_2sm(smem_u32(tmem_ptr_smem), Cfg::kTmemCols);
+            tmem_relinquish_2sm();
+        } else {
+            tmem_alloc(smem_u32(tmem_ptr_smem), Cfg::kTmemCols);
+            tmem_relinquish();
+        }
     }
     tc_fence_before_sync();
     __syncthreads();
+    if constexpr (CG == 2) cluster_sync_all();  // the peer's barriers exist before anything signals them
     tc_fence_after_sync();
     const uint32_t tmem_base = *tmem_ptr_smem;
 
+    auto tma_ld = [](uint32_t dst, const CUtensorMap* m, uint32_t bar, int c0, int c1, uint64_t pol) {
+        if constexpr (CG == 2) tma_load_2d_hint_2sm(dst, m, bar, c0, c1, pol);
+        else tma_load_2d_hint(dst, m, bar, c0, c1, pol);
+    };
     if (warp == 0) {
         // ============================== TMA producer ==============================
         if (lane == 0) {
             int stage = 0;
             uint32_t phase = 0;
-            for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+            for (int t = worker; t < num_tiles; t += num_workers) {
                 int m_blk, n_blk;
                 tile_coords(t, num_m, num_n, p.group_m, m_blk, n_blk);
-                const int m0 = m_blk * kBM, n0 = n_blk * BN;
+                const int m0 = m_blk * kTileM + cta_rank * kBM, n0 = n_blk * BN + cta_rank * Cfg::kBRows;
                 for (int kb = 0; kb < num_k; ++kb) {
                     const uint32_t full = bar_full + 8 * stage;
                     mbar_wait(bar_empty + 8 * stage, phase ^ 1);
-                    mbar_arrive_expect_tx(full, Cfg::kStageBytes);
+                    // pair: both CTAs' loads count on the leader's barrier, which expects both halves
+                    if (CG == 1 || cta_rank == 0) mbar_arrive_expect_tx(full, Cfg::kStageBytes * CG);
                     const uint32_t a_dst = smem_u32(smem + stage * Cfg::kStageBytes);
                     const uint32_t b_dst = a_dst + Cfg::kABytes;
                     const int k0 = kb * kBK;
                     if constexpr (!A_MN) {
-                        tma_load_2d_hint(a_dst, &tmA, full, k0, m0, p.a_policy);  // box {64 k, 128 m}
+                        tma_ld(a_dst, &tmA, full, k0, m0, p.a_policy);  // box {64 k, 128 m}
                     } else {
 #pragma unroll
                         for (int i = 0; i < kBM / 64; ++i)      // box {64 m, 64 k} per atom
-                            tma_load_2d_hint(a_dst + i * (kBK * 128), &tmA, full, m0 + 64 * i, k0, p.a_policy);
+                            tma_ld(a_dst + i * (kBK * 128), &tmA, full, m0 + 64 * i, k0, p.a_policy);
                     }
                     if constexpr (!B_MN) {
-                        tma_load_2d_hint(b_dst, &tmB, full, k0, n0, p.b_policy);  // box {64 k, BN n}
+                        tma_ld(b_dst, &tmB, full, k0, n0, p.b_policy);  // box {64 k, BN / CG n}
                     } else {
 #pragma unroll
-                        for (int i = 0; i < BN / 64; ++i)
-                            tma_load_2d_hint(b_dst + i * (kBK * 128), &tmB, full, n0 + 64 * i, k0, p.b_policy);
+                        for (int i = 0; i < Cfg::kBRows / 64; ++i)
+                            tma_ld(b_dst + i * (kBK * 128), &tmB, full, n0 + 64 * i, k0, p.b_policy);
                     }
                     if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
                 }
@@ -153,8 +171,8 @@ __device__ __forceinline__ void gemm_cta_body(const CUtensorMap& tmA, const CUte
         }
     } else if (warp == 1) {
         // ============================== MMA issuer ==============================
-        if (lane == 0) {
-            constexpr uint32_t idesc = make_idesc_bf16(kBM, BN, A_MN ? 1 : 0, B_MN ? 1 : 0);
+        if (lane == 0 && cta_rank == 0) {
+            constexpr uint32_t idesc = make_idesc_bf16(kTileM, BN, A_MN ? 1 : 0, B_MN ? 1 : 0);
             // K-major: 8-row groups are 1024 B apart (SBO), LBO unused inside one 128 B atom.
             // MN-major: 8 k-rows are 1024 B apart (SBO), 64-element MN atoms kBK*128 B apart (LBO).
             constexpr uint32_t a_lbo = A_MN ? kBK * 128 : 0, b_lbo = B_MN ? kBK * 128 : 0;
@@ -163,7 +181,7 @@ __device__ __forceinline__ void gemm_cta_body(const CUtensorMap& tmA, const CUte
             uint32_t phase = 0;
             int as = 0;
             uint32_t aphase = 0;
-            for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+            for (int t = worker; t < num_tiles; t += num_workers) {
                 mbar_wait(bar_tempty + 8 * as, aphase ^ 1);
                 tc_fence_after_sync();
                 const uint32_t d_tmem = tmem_base + as * BN;
@@ -176,12 +194,17 @@ __device__ __forceinline__ void gemm_cta_body(const CUtensorMap& tmA, const CUte
                     for (int k = 0; k < kBK / 16; ++k) {
                         const uint64_t da = make_smem_desc_sw128(a_addr + k * a_kstep, a_lbo, 1024);
                         const uint64_t db = make_smem_desc_sw128(b_addr + k * b_kstep, b_lbo, 1024);
-                        umma_f16_ss(d_tmem, da, db, idesc, (kb | k) != 0 ? 1u : 0u);
+                        if constexpr (CG == 2) umma_f16_ss_2sm(d_tmem, da, db, idesc, (kb | k) != 0 ? 1u : 0u);
+                        else umma_f16_ss(d_tmem, da, db, idesc, (kb | k) != 0 ? 1u : 0u);
                     }
-                    umma_commit(bar_empty + 8 * stage);  // smem slot free once these MMAs retire
+                    // smem slot free once these MMAs retire (pair: in both CTAs)
+                    if constexpr (CG == 2) umma_commit_2sm(bar_empty + 8 * stage, 3);
+                    else umma_commit(bar_empty + 8 * stage);
                     if (++stage == Cfg::kStages) { stage = 0; phase ^= 1; }
                 }
-                umma_commit(bar_tfull + 8 * as);  // accumulator complete
+                // accumulator complete
+                if constexpr (CG == 2) umma_commit_2sm(bar_tfull + 8 * as, 3);
+                else umma_commit(bar_tfull + 8 * as);
                 if (++as == 2) { as = 0; aphase ^= 1; }
             }
         }
@@ -200,10 +223,16 @@ __device__ __forceinline__ void gemm_cta_body(const CUtensorMap& tmA, const CUte
         int as = 0;
         uint32_t aphase = 0;
         uint32_t chunk_it = 0;
-        for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+        // The MMA issuer (pair: the leader's) learns that an accumulator stage was drained.
+        auto release_acc = [&](int stage_idx) {
+            tc_fence_before_sync();
+            if constexpr (CG == 2) mbar_arrive_cluster(mapa_shared(bar_tempty + 8 * stage_idx, 0));
+            else mbar_arrive(bar_tempty + 8 * stage_idx);
+        };
+        for (int t = worker; t < num_tiles; t += num_workers) {
             int m_blk, n_blk;
             tile_coords(t, num_m, num_n, p.group_m, m_blk, n_blk);
-            const int m0 = m_blk * kBM, n0 = n_blk * BN;
+            const int m0 = m_blk * kTileM + cta_rank * kBM, n0 = n_blk * BN;
             mbar_wait(bar_tfull + 8 * as, aphase);
             tc_fence_after_sync();
 #pragma unroll 1
@@ -212,10 +241,7 @@ __device__ __forceinline__ void gemm_cta_body(const CUtensorMap& tmA, const CUte
                 const bool last = (c == BN / kEpiCols - 1);
                 if (nc >= p.N) {
                     // chunk entirely right of the matrix edge: nothing to store
-                    if (last) {
-                        tc_fence_before_sync();
-                        mbar_arrive(bar_tempty + 8 * as);
-                    }
+                    if (last) release_acc(as);
                     continue;
                 }
                 const int buf = chunk_it & 1;
@@ -235,11 +261,7 @@ __device__ __forceinline__ void gemm_cta_body(const CUtensorMap& tmA, const CUte
                 uint32_t acc[32];
                 tmem_ld_32x32b_x32(tmem_base + as * BN + c * kEpiCols + ((warp_e * 32u) << 16), acc);
                 tmem_ld_wait();
-                if (last) {
-                    // accumulator fully drained into registers: hand the TMEM stage back
-                    tc_fence_before_sync();
-                    mbar_arrive(bar_tempty + 8 * as);
-                }
+                if (last) release_acc(as);  // accumulator fully drained into registers
                 uint32_t auxw[16];
                 if (aux_in) {
                     mbar_wait(bar_aux + 8 * buf, aux_phase);
@@ -308,9 +330,13 @@ __device__ __forceinline__ void gemm_cta_body(const CUtensorMap& tmA, const CUte
 
     tc_fence_before_sync();
     __syncthreads();
+    if constexpr (CG == 2) cluster_sync_all();  // no CTA leaves while its peer may still signal it
     tc_fence_after_sync();
     fusion.finish();
-    if (warp == 2) tmem_dealloc(tmem_base, Cfg::kTmemCols);
+    if (warp == 2) {
+        if constexpr (CG == 2) tmem_dealloc_2sm(tmem_base, Cfg::kTmemCols);
+        else tmem_dealloc(tmem_base, Cfg::kTmemCols);
+    }
 }
 
 template <int BN, bool A_MN, bool B_MN>
@@ -321,6 +347,17 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA,
                          const __grid_constant__ CUtensorMap tmAux, const GemmParams p) {
     NoFusion nf;
     gemm_cta_body<BN, A_MN, B_MN, NoFusion>(tmA, tmB, tmC, tmAux, p, nf);
+}
+
+// CTA-pair variant: cluster (2,1,1), one 256 x 256 tile per pair, tcgen05.mma.cta_group::2.
+template <bool A_MN, bool B_MN>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kNumThreads, 1)
+gemm_bf16_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap tmA,
+                              const __grid_constant__ CUtensorMap tmB,
+                              const __grid_constant__ CUtensorMap tmC,
+                              const __grid_constant__ CUtensorMap tmAux, const GemmParams p) {
+    NoFusion nf;
+    gemm_cta_body<256, A_MN, B_MN, NoFusion, 2>(tmA, tmB, tmC, tmAux, p, nf);
 }
 
 // ------------------------------------------------------------------------------------------

@@ -28,6 +28,7 @@ _SIGNATURES = {
     "dlbb_gemm_bf16_simt": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int64, c_int64,
                                     c_int64, c_int, c_int, c_int, c_void_p, c_int64, c_void_p]),
     "dlbb_gemm_set_tile_n": (None, [c_int]),
+    "dlbb_gemm_set_pair_mode": (None, [c_int]),
     "dlbb_layernorm_fwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int,
                                    c_float, c_void_p]),
     "dlbb_layernorm_bwd_scratch_bytes": (c_size_t, [c_int, c_int]),

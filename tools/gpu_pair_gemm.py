@@ -1,0 +1,148 @@
+#!/usr/bin/env python3
+"""CTA-pair GEMM (tcgen05.mma.cta_group::2) self-check: numerics of every layout / epilogue / ragged
+shape against fp32 PyTorch, then timing on the 7B model's shapes against the one-CTA kernel and
+cuBLAS.  Run under gpurun (wrap in `timeout`); writes gpurun_out/pair_gemm.json."""
+import json, os, sys
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+from distributed_llm_backend_benchmark_b200 import ops, _lib
+
+dev = torch.device("cuda:0")
+torch.manual_seed(0)
+lib = _lib.load()
+res = {"numerics": [], "perf": []}
+ok_all = True
+
+
+def relerr(a, b):
+    a, b = a.float(), b.float()
+    return ((a - b).norm() / (b.norm() + 1e-30)).item()
+
+
+def case(M, N, K, ta, tb, epi, pad=0):
+    for mode in (1,):
+        case_mode(M, N, K, ta, tb, epi, pad, mode)
+
+
+def case_mode(M, N, K, ta, tb, epi, pad, mode):
+    global ok_all
+    a_shape = (K, M) if ta else (M, K)
+    b_shape = (N, K) if tb else (K, N)
+
+    def mk(shape, scale=1.0):
+        full = torch.randn(shape[0], shape[1] + pad, device=dev, dtype=torch.float32) * scale
+        return full.bfloat16()[:, :shape[1]]
+    a, b = mk(a_shape), mk(b_shape, 0.5)
+    A = (a.t() if ta else a).float(); B = (b.t() if tb else b).float()
+    acc = A @ B
+    aux = None
+    if epi == "gelu":
+        aux = torch.zeros(M, N + pad, device=dev, dtype=torch.bfloat16)[:, :N]; ref = ops.gelu_ref(acc)
+    elif epi == "add":
+        aux = mk((M, N), 10.0); ref = acc + aux.float()
+    elif epi == "mul_dgelu":
+        aux = mk((M, N)); ref = acc * ops.dgelu_ref(aux.float())
+    else:
+        ref = acc
+    out = torch.full((M, N + pad), 7.0, device=dev, dtype=torch.bfloat16)[:, :N]
+    lib.dlbb_gemm_set_pair_mode(mode)
+    ops.matmul(a, b, transpose_a=ta, transpose_b=tb, epilogue=epi, aux=aux, out=out)
+    torch.cuda.synchronize()
+    e = relerr(out, ref)
+    e_aux = relerr(aux, acc) if epi == "gelu" else 0.0
+    # the one-CTA kernel must agree bit for bit (same k order, same fp32 accumulation)
+    out1 = torch.empty_like(out)
+    aux1 = torch.zeros_like(aux) if epi == "gelu" else aux
+    lib.dlbb_gemm_set_pair_mode(0)
+    ops.matmul(a, b, transpose_a=ta, transpose_b=tb, epilogue=epi, aux=aux1, out=out1)
+    torch.cuda.synchronize()
+    same = bool(torch.equal(out, out1))
+    ok = e < 6e-3 and e_aux < 6e-3
+    ok_all &= ok
+    rec = dict(mode=mode, M=M, N=N, K=K, ta=ta, tb=tb, epi=epi, pad=pad, relerr=e, relerr_aux=e_aux, bitwise_vs_1cta=same, ok=ok)
+    res["numerics"].append(rec)
+    print(("PASS " if ok else "FAIL ") + json.dumps(rec), flush=True)
+
+
+try:
+    case(256, 256, 64, False, True, None)           # one pair, one k block
+    case(256, 256, 512, False, True, None)          # ring wrap-around
+    for ta in (False, True):
+        for tb in (False, True):
+            case(512, 768, 320, ta, tb, None)
+    for epi in ("gelu", "add", "mul_dgelu"):
+        case(512, 768, 256, False, False, epi)
+        case(768, 512, 256, True, False, epi)
+    case(300, 520, 200, False, False, "add", pad=8)  # ragged: second CTA of the pair partly / fully outside
+    case(200, 136, 72, True, True, None, pad=16)
+    case(130, 264, 24, True, False, None)
+    case(1000, 1000, 1000, False, True, "gelu")
+    case(4096, 4096, 512, False, False, None)        # many tiles per pair
+    case(2048, 8192, 1024, True, False, "add")
+    case(38400, 512, 128, False, True, None)         # more m-blocks than pairs
+except Exception as e:
+    ok_all = False
+    res["exception"] = repr(e)
+    print("EXCEPTION", repr(e), flush=True)
+
+
+def bench(fn, iters=20, warm=5):
+    for _ in range(warm): fn()
+    torch.cuda.synchronize()
+    s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    s.record()
+    for _ in range(iters): fn()
+    e.record(); torch.cuda.synchronize()
+    return s.elapsed_time(e) / iters
+
+
+if ok_all:
+    # The GPU runs at its power cap and drifts by +-10% over seconds, so variants are interleaved
+    # round-robin and the median of the rounds is reported.
+    import statistics
+    H, F, T = 4096, 16384, 4096
+    shapes = [("qkv_fwd", T, 3 * H, H, False, False, None), ("out_fwd", T, H, H, False, False, "add"),
+              ("up_fwd", T, F, H, False, False, "gelu"), ("down_fwd", T, H, F, False, False, "add"),
+              ("down_dgrad", T, F, H, False, True, "mul_dgelu"), ("up_dgrad", T, H, F, False, True, None),
+              ("down_wgrad", F, H, T, True, False, None), ("up_wgrad", H, F, T, True, False, None)]
+    rounds = int(os.environ.get("ROUNDS", "7"))
+    for name, M, N, K, ta, tb, epi in shapes:
+        a = torch.randn((K, M) if ta else (M, K), device=dev).bfloat16()
+        b = torch.randn((N, K) if tb else (K, N), device=dev).bfloat16()
+        out = torch.empty(M, N, device=dev, dtype=torch.bfloat16)
+        aux = torch.randn(M, N, device=dev).bfloat16() if epi else None
+        A = a.t() if ta else a; B = b.t() if tb else b
+        variants = {}
+        for mode, key in ((0, "one_cta"), (1, "pair")):
+            def plain(mode=mode):
+                lib.dlbb_gemm_set_pair_mode(mode)
+                ops.matmul(a, b, transpose_a=ta, transpose_b=tb, out=out)
+            variants[key] = plain
+            if epi:
+                def fused(mode=mode):
+                    lib.dlbb_gemm_set_pair_mode(mode)
+                    ops.matmul(a, b, transpose_a=ta, transpose_b=tb, epilogue=epi, aux=aux, out=out)
+                variants[key + "_epi"] = fused
+            if epi == "gelu":
+                def gelu_only(mode=mode):   # math only: no pre-activation store
+                    lib.dlbb_gemm_set_pair_mode(mode)
+                    ops.matmul(a, b, transpose_a=ta, transpose_b=tb, epilogue="gelu", aux=None, out=out)
+                variants[key + "_gelu_noaux"] = gelu_only
+        variants["cublas"] = lambda: torch.matmul(A, B, out=out)
+        samples = {k: [] for k in variants}
+        for r in range(rounds):
+            for k, fn in variants.items():
+                samples[k].append(bench(fn, iters=10, warm=2))
+        row = dict(name=name, M=M, N=N, K=K, ta=ta, tb=tb, epi=epi)
+        for k, v in samples.items():
+            row[k + "_ms"] = round(statistics.median(v), 5)
+        for k in ("one_cta", "pair", "cublas"):
+            row[k + "_tflops"] = round(2.0 * M * N * K / row[k + "_ms"] / 1e9, 1)
+        res["perf"].append(row); print("PERF", json.dumps(row), flush=True)
+    lib.dlbb_gemm_set_pair_mode(-1)
+
+res["ok"] = ok_all
+os.makedirs("gpurun_out", exist_ok=True)
+json.dump(res, open("gpurun_out/pair_gemm.json", "w"), indent=1)
+print("PAIR GEMM", "OK" if ok_all else "FAILED")
+sys.exit(0 if ok_all else 1)
