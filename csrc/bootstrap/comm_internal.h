@@ -44,6 +44,20 @@ struct CommDev {
     uint32_t* tile_flags[DLBB_MAX_RANKS];
 };
 
+// The same logical user buffer on every rank, as mapped in this process (peer_registry.cpp).
+struct PeerView {
+    char* ptr[DLBB_MAX_RANKS];
+};
+struct PeerRegistry;
+
+}  // namespace dlbb
+
+struct dlbb_comm;
+namespace dlbb {
+PeerRegistry* peer_registry_create(dlbb_comm* c);
+void peer_registry_destroy(PeerRegistry* r);
+bool peer_registry_usable(const PeerRegistry* r);
+int peer_registry_resolve(dlbb_comm* c, PeerRegistry* r, const void* ptr, size_t bytes, PeerView* pv, bool* all_ok);
 }  // namespace dlbb
 
 struct dlbb_comm {
@@ -61,5 +75,7 @@ struct dlbb_comm {
     int ctas = 0;                  // 0 = auto
     size_t oneshot_max = 0;        // 0 = auto
     int default_algo = 0;          // DLBB_ALGO: what DLBB_ALGO_AUTO resolves to (0 = size-based choice)
+    dlbb::PeerRegistry* reg = nullptr;   // zero-copy access to the peers' ordinary allocations
+    size_t zero_copy_min = 0;      // messages of at least this many bytes try the zero-copy kernels (0 = never)
     dlbb::CommDev dev{};
 };

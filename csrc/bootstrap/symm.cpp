@@ -357,11 +357,21 @@ int dlbb_comm_create(int rank, int world, int device, const char* job, size_t st
     if (e) {
         const std::string a(e);
         c->default_algo = a == "oneshot" ? DLBB_ALGO_ONESHOT : a == "twoshot" ? DLBB_ALGO_TWOSHOT
-                        : a == "nvls" ? DLBB_ALGO_NVLS : DLBB_ALGO_AUTO;
+                        : a == "nvls" ? DLBB_ALGO_NVLS : a == "direct" ? DLBB_ALGO_DIRECT : DLBB_ALGO_AUTO;
+    }
+    // Zero-copy path for large messages on ordinary allocations (peer_registry.cpp); DLBB_ZEROCOPY_MIN_BYTES=0 disables.
+    e = getenv("DLBB_ZEROCOPY_MIN_BYTES");
+    c->zero_copy_min = e ? static_cast<size_t>(atoll(e)) : (static_cast<size_t>(16) << 20);
+    if (world > 1 && c->zero_copy_min > 0) {
+        c->reg = dlbb::peer_registry_create(c);
+        if (!dlbb::peer_registry_usable(c->reg)) c->zero_copy_min = 0;
+    } else {
+        c->zero_copy_min = 0;
     }
     if (getenv("DLBB_LOG_LEVEL") && rank == 0)
-        fprintf(stderr, "dlbb: comm up, %d ranks, granularity %zu MiB, staging 2x%zu MiB, multicast %s\n", world,
-                c->gran >> 20, c->stage_bytes >> 20, c->mc_supported ? "on" : "off");
+        fprintf(stderr, "dlbb: comm up, %d ranks, granularity %zu MiB, staging 2x%zu MiB, multicast %s, zero-copy %s\n",
+                world, c->gran >> 20, c->stage_bytes >> 20, c->mc_supported ? "on" : "off",
+                c->zero_copy_min ? "on" : "off");
     *out = c;
     return 0;
 }
@@ -370,6 +380,7 @@ int dlbb_comm_destroy(dlbb_comm_t* c) {
     if (!c) return 0;
     for (int i = static_cast<int>(c->segs.size()) - 1; i >= 0; --i)
         if (c->segs[i].live) dlbb_symm_free(c, i);
+    dlbb::peer_registry_destroy(c->reg);
     delete c->bs;
     delete c;
     return 0;
@@ -393,5 +404,9 @@ int dlbb_comm_host_allgather(dlbb_comm_t* c, const void* in, void* out, size_t b
 
 void dlbb_comm_set_ctas(dlbb_comm_t* c, int ctas) { c->ctas = ctas < 0 ? 0 : (ctas > dlbb::kMaxCtas ? dlbb::kMaxCtas : ctas); }
 void dlbb_comm_set_oneshot_max_bytes(dlbb_comm_t* c, size_t bytes) { c->oneshot_max = bytes; }
+void dlbb_comm_set_zero_copy_min_bytes(dlbb_comm_t* c, size_t bytes) {
+    c->zero_copy_min = dlbb::peer_registry_usable(c->reg) ? bytes : 0;
+}
+size_t dlbb_comm_zero_copy_min_bytes(const dlbb_comm_t* c) { return c->zero_copy_min; }
 
 }  // extern "C"

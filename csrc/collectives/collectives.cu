@@ -84,9 +84,23 @@ __global__ void barrier_kernel(CommDev c, int bank, uint32_t epoch) { row_barrie
 
 // ------------------------------------------------------------------------------------------
 // K6/K7/K9/K10/K11: data movement (all-gather, broadcast, gather, scatter, all-to-all, sendrecv)
+//
+// Zero-copy form (direct != 0, peer_registry.cpp): the pull pieces address the peers' own source tensors
+// (pv.ptr[peer] + a_off), nothing is packed, and a second barrier keeps every rank inside the kernel - and its
+// stream from overwriting the source - until all peers have read it.  CTA b only meets CTA b of the peers.
 __global__ void __launch_bounds__(kCollThreads)
 move_kernel(CommDev c, const char* __restrict__ src, char* __restrict__ dst, PieceList pack, PieceList pull,
-            ViewDev view, int elem_size, int64_t stage_off, int bank, uint32_t epoch) {
+            ViewDev view, int elem_size, int64_t stage_off, int bank, uint32_t epoch, const __grid_constant__ PeerView pv, int direct) {
+    if (direct) {
+        row_barrier(c, bank, blockIdx.x, epoch);   // the peers' kernels run, so their sources are final
+        for (int i = 0; i < pull.count; ++i) {
+            const Piece& pc = pull.p[i];
+            const char* from = pv.ptr[pc.peer] + pc.a_off;
+            if (from != dst + pc.b_off) grid_copy_bytes<true>(dst + pc.b_off, from, pc.n);
+        }
+        row_barrier(c, bank, blockIdx.x, epoch + 1);
+        return;
+    }
     char* my_stage = c.stage[c.rank] + stage_off;
     for (int i = 0; i < pack.count; ++i) {
         const Piece& pc = pack.p[i];
@@ -112,6 +126,80 @@ move_kernel(CommDev c, const char* __restrict__ src, char* __restrict__ dst, Pie
         const Piece& pc = pull.p[i];
         grid_copy_bytes<true>(dst + pc.b_off, c.stage[pc.peer] + stage_off + pc.a_off, pc.n);
     }
+}
+
+// ------------------------------------------------------------------------------------------
+// K7 on more than two ranks: broadcast through the switch.  Pulling from the root costs the root's link
+// (world-1) x the message; instead the root writes its tensor ONCE to the multicast mapping of the staging
+// area (multimem.st - NVSwitch replicates it into every rank's staging), then every other rank copies its
+// local staging copy into the user tensor.  CTA b owns byte range b and only meets CTA b of the peers.
+constexpr int kBcChunkVecs = 16384;   // 256 KiB sub-chunks: receivers copy chunk k while the root multicasts chunk k+1
+constexpr int kBcFlagBank = 4;        // one-directional "chunk k is in your staging" flags (shared with the pipelined all-reduce)
+
+__global__ void __launch_bounds__(kCollThreads)
+broadcast_nvls_kernel(CommDev c, const char* __restrict__ src, char* __restrict__ dst, int64_t bytes, int root,
+                      int64_t stage_off, uint32_t flag_base, int nchunks, int bank, uint32_t end_epoch) {
+    const int64_t nvec = bytes >> 4;
+    const int64_t per = (nvec + gridDim.x - 1) / gridDim.x;
+    const int64_t v_lo = std::min<int64_t>((int64_t)blockIdx.x * per, nvec);
+    const int64_t v_hi = std::min<int64_t>(v_lo + per, nvec);
+    const int64_t tail_lo = nvec << 4;   // < 16 trailing bytes travel with chunk 0 of CTA 0 as plain peer stores
+    const int row = blockIdx.x;
+    const char* mine = c.stage[c.rank] + stage_off;
+    const bool src_vec = (reinterpret_cast<uintptr_t>(src) & 15) == 0, dst_vec = (reinterpret_cast<uintptr_t>(dst) & 15) == 0;
+    for (int k = 0; k < nchunks; ++k) {
+        const int64_t c_lo = std::min<int64_t>(v_lo + (int64_t)k * kBcChunkVecs, v_hi);
+        const int64_t c_hi = std::min<int64_t>(c_lo + kBcChunkVecs, v_hi);
+        if (c.rank == root) {
+            char* mc = c.stage_mc + stage_off;
+            if (src_vec) {
+                for (int64_t i0 = c_lo + threadIdx.x; i0 < c_hi; i0 += (int64_t)blockDim.x * kU) {
+                    uint4 v[kU];
+#pragma unroll
+                    for (int u = 0; u < kU; ++u)
+                        if (i0 + u * blockDim.x < c_hi) v[u] = ld_stream_v4(src + ((i0 + u * blockDim.x) << 4));
+#pragma unroll
+                    for (int u = 0; u < kU; ++u)
+                        if (i0 + u * blockDim.x < c_hi) mm_st_v4(mc + ((i0 + u * blockDim.x) << 4), v[u]);
+                }
+            } else {
+                for (int64_t i = c_lo + threadIdx.x; i < c_hi; i += blockDim.x) {
+                    uint4 v;
+                    char* vb = reinterpret_cast<char*>(&v);
+#pragma unroll
+                    for (int b = 0; b < 16; ++b) vb[b] = src[(i << 4) + b];
+                    mm_st_v4(mc + (i << 4), v);
+                }
+            }
+            if (row == 0 && k == 0)
+                for (int64_t b = tail_lo + threadIdx.x; b < bytes; b += blockDim.x)
+                    for (int p = 0; p < c.world; ++p) c.stage[p][stage_off + b] = src[b];
+            __syncthreads();
+            if (threadIdx.x < c.world && threadIdx.x != root)
+                st_release_sys(pad_slot(c, threadIdx.x, kBcFlagBank, row, root), flag_base + k + 1);
+        } else {
+            if (threadIdx.x == 0) wait_flag(pad_slot(c, c.rank, kBcFlagBank, row, root), flag_base + k + 1, root);
+            __syncthreads();
+            if (dst_vec) {
+                for (int64_t i0 = c_lo + threadIdx.x; i0 < c_hi; i0 += (int64_t)blockDim.x * kU) {
+                    uint4 v[kU];
+#pragma unroll
+                    for (int u = 0; u < kU; ++u)   // written through the switch during this kernel: bypass L1
+                        if (i0 + u * blockDim.x < c_hi) v[u] = ld_peer_v4(mine + ((i0 + u * blockDim.x) << 4));
+#pragma unroll
+                    for (int u = 0; u < kU; ++u)
+                        if (i0 + u * blockDim.x < c_hi) st_v4(dst + ((i0 + u * blockDim.x) << 4), v[u]);
+                }
+            } else {
+                for (int64_t b = (c_lo << 4) + threadIdx.x; b < (c_hi << 4); b += blockDim.x) dst[b] = ld_peer_scalar(mine + b);
+            }
+            if (row == 0 && k == 0)
+                for (int64_t b = tail_lo + threadIdx.x; b < bytes; b += blockDim.x) dst[b] = ld_peer_scalar(mine + b);
+        }
+    }
+    // The root never waits inside the loop; this closing barrier keeps it from running ahead and reusing the
+    // staging region while a receiver is still copying out of it.
+    row_barrier(c, bank, row, end_epoch);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -163,14 +251,14 @@ __device__ __forceinline__ void pack_typed(T* stage, const T* __restrict__ src, 
 // Reduce kU vector positions (i0 + u*stride, u < kU) across all ranks, in rank order, so every rank
 // computes bit-identical results.  All kU loads of one peer are issued before any is consumed.
 template <typename T, int OP>
-__device__ __forceinline__ void reduce_batch(const CommDev& c, int64_t base_byte_off, int64_t i0, int64_t stride,
-                                             int64_t nvec, uint4 (&out)[kU]) {
+__device__ __forceinline__ void reduce_batch(const CommDev& c, char* const (&bases)[DLBB_MAX_RANKS], int64_t base_byte_off,
+                                             int64_t i0, int64_t stride, int64_t nvec, uint4 (&out)[kU]) {
     constexpr int VE = 16 / sizeof(T);
     using A = typename Acc<T>::type;
     A acc[kU][VE];
     for (int p = 0; p < c.world; ++p) {
         uint4 buf[kU];
-        const char* sp = c.stage[p] + base_byte_off;
+        const char* sp = bases[p] + base_byte_off;
 #pragma unroll
         for (int u = 0; u < kU; ++u)
             if (i0 + u * stride < nvec) buf[u] = ld_peer_v4(sp + ((i0 + u * stride) << 4));
@@ -195,32 +283,28 @@ __device__ __forceinline__ void reduce_batch(const CommDev& c, int64_t base_byte
 }
 
 template <typename T, int OP>
-__device__ __forceinline__ typename Acc<T>::type reduce_scalar(const CommDev& c, int64_t stage_byte_off) {
+__device__ __forceinline__ void reduce_batch(const CommDev& c, int64_t base_byte_off, int64_t i0, int64_t stride,
+                                             int64_t nvec, uint4 (&out)[kU]) {
+    reduce_batch<T, OP>(c, c.stage, base_byte_off, i0, stride, nvec, out);
+}
+
+template <typename T, int OP>
+__device__ __forceinline__ typename Acc<T>::type reduce_scalar(const CommDev& c, char* const (&bases)[DLBB_MAX_RANKS],
+                                                               int64_t byte_off) {
     using A = typename Acc<T>::type;
-    A acc = to_acc<T>(ld_peer_scalar(reinterpret_cast<const T*>(c.stage[0] + stage_byte_off)));
+    A acc = to_acc<T>(ld_peer_scalar(reinterpret_cast<const T*>(bases[0] + byte_off)));
     for (int p = 1; p < c.world; ++p)
-        acc = red_op<OP, A>(acc, to_acc<T>(ld_peer_scalar(reinterpret_cast<const T*>(c.stage[p] + stage_byte_off))));
+        acc = red_op<OP, A>(acc, to_acc<T>(ld_peer_scalar(reinterpret_cast<const T*>(bases[p] + byte_off))));
     return acc;
 }
 
-// ------------------------------------------------------------------------------------------
-// K2/K5/K8: single-barrier reductions (one-shot all-reduce, reduce, reduce-scatter).
-// Every rank packs `pack` pieces; ranks with red_n > 0 reduce stage elements
-// [red_off, red_off + red_n) over all ranks into dst (+ extra, if given).
+// Reduce red_n elements at byte offset base_b of every rank's buffer into dst (+ extra), whole grid.
 template <typename T, int OP>
-__global__ void __launch_bounds__(kCollThreads)
-reduce_kernel(CommDev c, const T* __restrict__ src, T* __restrict__ dst, const T* __restrict__ extra, PieceList pack,
-              ViewDev view, int64_t red_off, int64_t red_n, int64_t stage_off, int bank, uint32_t epoch) {
+__device__ __forceinline__ void reduce_range(const CommDev& c, char* const (&bases)[DLBB_MAX_RANKS], T* __restrict__ dst,
+                                             const T* __restrict__ extra, int64_t base_b, int64_t red_n, int64_t tid,
+                                             int64_t nth) {
     constexpr int VE = 16 / sizeof(T);
     using A = typename Acc<T>::type;
-    const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    const int64_t nth = (int64_t)gridDim.x * blockDim.x;
-    T* my_stage = reinterpret_cast<T*>(c.stage[c.rank] + stage_off);
-    for (int i = 0; i < pack.count; ++i)
-        pack_typed<T>(my_stage + pack.p[i].b_off, src, view, pack.p[i].a_off, pack.p[i].n, tid, nth);
-    grid_barrier(c, bank, gridDim.x, epoch);
-    if (red_n <= 0) return;
-    const int64_t base_b = stage_off + red_off * (int64_t)sizeof(T);
     const bool vec_ok = (base_b & 15) == 0 && (reinterpret_cast<uintptr_t>(dst) & 15) == 0 &&
                         (extra == nullptr || (reinterpret_cast<uintptr_t>(extra) & 15) == 0);
     int64_t done = 0;
@@ -228,7 +312,7 @@ reduce_kernel(CommDev c, const T* __restrict__ src, T* __restrict__ dst, const T
         const int64_t nvec = red_n / VE;
         for (int64_t i0 = tid; i0 < nvec; i0 += nth * kU) {
             uint4 o[kU];
-            reduce_batch<T, OP>(c, base_b, i0, nth, nvec, o);
+            reduce_batch<T, OP>(c, bases, base_b, i0, nth, nvec, o);
 #pragma unroll
             for (int u = 0; u < kU; ++u) {
                 const int64_t i = i0 + u * nth;
@@ -247,10 +331,101 @@ reduce_kernel(CommDev c, const T* __restrict__ src, T* __restrict__ dst, const T
         done = nvec * VE;
     }
     for (int64_t i = done + tid; i < red_n; i += nth) {
-        A a = reduce_scalar<T, OP>(c, base_b + i * (int64_t)sizeof(T));
+        A a = reduce_scalar<T, OP>(c, bases, base_b + i * (int64_t)sizeof(T));
         if (extra) a += to_acc<T>(extra[i]);
         dst[i] = from_acc<T>(a);
     }
+}
+
+// ------------------------------------------------------------------------------------------
+// K2/K5/K8: single-barrier reductions (one-shot all-reduce, reduce, reduce-scatter).
+// Every rank packs `pack` pieces; ranks with red_n > 0 reduce stage elements
+// [red_off, red_off + red_n) over all ranks into dst (+ extra, if given).
+// Zero-copy form (direct != 0): nothing is packed, the reduction reads elements [red_off, red_off + red_n) of the
+// peers' own source tensors (pv), and a closing barrier keeps the sources untouched until everyone is done.
+template <typename T, int OP>
+__global__ void __launch_bounds__(kCollThreads)
+reduce_kernel(CommDev c, const T* __restrict__ src, T* __restrict__ dst, const T* __restrict__ extra, PieceList pack,
+              ViewDev view, int64_t red_off, int64_t red_n, int64_t stage_off, int bank, uint32_t epoch,
+              const __grid_constant__ PeerView pv, int direct) {
+    const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t nth = (int64_t)gridDim.x * blockDim.x;
+    if (direct) {
+        row_barrier(c, bank, blockIdx.x, epoch);
+    } else {
+        T* my_stage = reinterpret_cast<T*>(c.stage[c.rank] + stage_off);
+        for (int i = 0; i < pack.count; ++i)
+            pack_typed<T>(my_stage + pack.p[i].b_off, src, view, pack.p[i].a_off, pack.p[i].n, tid, nth);
+        grid_barrier(c, bank, gridDim.x, epoch);
+    }
+    const int64_t red_b = red_off * (int64_t)sizeof(T);
+    if (red_n > 0) {
+        if (direct) reduce_range<T, OP>(c, pv.ptr, dst, extra, red_b, red_n, tid, nth);
+        else reduce_range<T, OP>(c, c.stage, dst, extra, stage_off + red_b, red_n, tid, nth);
+    }
+    if (direct) row_barrier(c, bank, blockIdx.x, epoch + 1);
+}
+
+// ------------------------------------------------------------------------------------------
+// K3 zero-copy: in-place two-shot all-reduce directly on the ranks' own tensors (pv, peer_registry.cpp).
+// CTA b owns range b on every rank; inside it rank r reduces its 1/world share out of all ranks' tensors
+// (loads from every peer in flight at once, summed in rank order -> bit-identical everywhere) and stores the
+// result into all ranks' tensors.  No pack, no unpack: the only HBM traffic is the NVLink traffic itself.
+// Rank q's share-r elements are read and written by rank r only, so in-place is race-free between the barriers.
+constexpr int kUD = 2;            // vectors per peer in flight per thread ...
+constexpr int kDirectMaxWorld = 8;   // ... times at most this many peers (one NVSwitch domain), all in registers
+
+template <typename T, int OP>
+__global__ void __launch_bounds__(kCollThreads)
+allreduce_direct_kernel(CommDev c, const __grid_constant__ PeerView pv, int64_t n, int bank, uint32_t epoch) {
+    constexpr int VE = 16 / sizeof(T);
+    using A = typename Acc<T>::type;
+    const int64_t nvec = n / VE;   // n is a multiple of VE * world (the host sends the tail through staging)
+    const int64_t per = (nvec + gridDim.x - 1) / gridDim.x;
+    const int64_t v_lo = std::min<int64_t>((int64_t)blockIdx.x * per, nvec);
+    const int64_t v_hi = std::min<int64_t>(v_lo + per, nvec);
+    const int64_t share = (v_hi - v_lo + c.world - 1) / c.world;
+    const int64_t s_lo = std::min<int64_t>(v_lo + c.rank * share, v_hi);
+    const int64_t s_hi = std::min<int64_t>(s_lo + share, v_hi);
+    row_barrier(c, bank, blockIdx.x, epoch);
+    for (int64_t i0 = s_lo + threadIdx.x; i0 < s_hi; i0 += (int64_t)blockDim.x * kUD) {
+        uint4 buf[kDirectMaxWorld][kUD];
+#pragma unroll
+        for (int p = 0; p < kDirectMaxWorld; ++p) {
+            if (p < c.world) {
+#pragma unroll
+                for (int u = 0; u < kUD; ++u)
+                    if (i0 + u * blockDim.x < s_hi) buf[p][u] = ld_peer_v4(pv.ptr[p] + ((i0 + u * blockDim.x) << 4));
+            }
+        }
+        uint4 o[kUD];
+#pragma unroll
+        for (int u = 0; u < kUD; ++u) {
+            A acc[VE];
+#pragma unroll
+            for (int p = 0; p < kDirectMaxWorld; ++p) {
+                if (p < c.world) {
+                    const T* t = reinterpret_cast<const T*>(&buf[p][u]);
+#pragma unroll
+                    for (int e = 0; e < VE; ++e) {
+                        const A x = to_acc<T>(t[e]);
+                        acc[e] = (p == 0) ? x : red_op<OP, A>(acc[e], x);
+                    }
+                }
+            }
+            T* ot = reinterpret_cast<T*>(&o[u]);
+#pragma unroll
+            for (int e = 0; e < VE; ++e) ot[e] = from_acc<T>(acc[e]);
+        }
+#pragma unroll 1
+        for (int p = 0; p < c.world; ++p) {
+            char* qp = pv.ptr[(c.rank + p) % c.world];   // spread the store targets over the peers
+#pragma unroll
+            for (int u = 0; u < kUD; ++u)
+                if (i0 + u * blockDim.x < s_hi) st_v4(qp + ((i0 + u * blockDim.x) << 4), o[u]);
+        }
+    }
+    row_barrier(c, bank, blockIdx.x, epoch + 1);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -274,11 +449,35 @@ template <> struct MmReduce<float> {
     __device__ static uint4 ld(const void* p) { return mm_ld_reduce_add_f32(p); }
 };
 
+// multimem.ld_reduce answers in ~10 us under load (measured: root-pull bandwidth grows linearly with the CTA count,
+// 167 -> 420 GB/s from 32 to 128 CTAs at 8 vectors per thread), so the loops that are nothing but ld_reduce keep
+// twice as many requests in flight per thread as the peer-load loops.
+constexpr int kUR = 16;
+
+// dst[i] = o (+ extra[i]) for one 16-byte vector of T; scalar stores when dst / extra are not 16 B aligned.
+template <typename T>
+__device__ __forceinline__ void store_result_vec(T* __restrict__ dst, const T* __restrict__ extra, int64_t i, uint4 o,
+                                                 bool dst_vec) {
+    constexpr int VE = 16 / sizeof(T);
+    if (extra) {
+        T* ot = reinterpret_cast<T*>(&o);
+#pragma unroll
+        for (int e = 0; e < VE; ++e) ot[e] = from_acc<T>(to_acc<T>(ot[e]) + to_acc<T>(extra[i * VE + e]));
+    }
+    if (dst_vec) {
+        st_v4(reinterpret_cast<uint4*>(dst) + i, o);
+    } else {
+        const T* ot = reinterpret_cast<const T*>(&o);
+#pragma unroll
+        for (int e = 0; e < VE; ++e) dst[i * VE + e] = ot[e];
+    }
+}
+
 template <typename T, int OP, bool NVLS>
 __global__ void __launch_bounds__(kCollThreads)
 allreduce_twoshot_kernel(CommDev c, const T* __restrict__ src, T* __restrict__ dst, const T* __restrict__ extra,
                          ViewDev view, int64_t src_off, int64_t n, int64_t in_off, int64_t out_off, int bank,
-                         uint32_t epoch) {
+                         uint32_t epoch, int root) {
     constexpr int VE = 16 / sizeof(T);
     using A = typename Acc<T>::type;
     // range of this CTA, in vectors; n is a multiple of VE * world (host pads the tail separately)
@@ -290,6 +489,27 @@ allreduce_twoshot_kernel(CommDev c, const T* __restrict__ src, T* __restrict__ d
     T* my_in = reinterpret_cast<T*>(c.stage[c.rank] + in_off);
     pack_typed<T>(my_in + v_lo * VE, src, view, src_off + v_lo * VE, cnt * VE, threadIdx.x, blockDim.x);
     row_barrier(c, bank, blockIdx.x, epoch);
+    if constexpr (NVLS && MmReduce<T>::ok) {
+        if (root >= 0) {
+            // Reduce-to-root through the switch: the root alone issues multimem.ld_reduce over the whole range and
+            // writes the user tensor directly - every rank's staging leaves its GPU once, the root receives the
+            // message once, and there is neither an out-staging hop nor an unpack.
+            if (c.rank == root) {
+                const bool dv = (reinterpret_cast<uintptr_t>(dst) & 15) == 0;
+                for (int64_t i0 = v_lo + threadIdx.x; i0 < v_hi; i0 += (int64_t)blockDim.x * kUR) {
+                    uint4 o[kUR];
+#pragma unroll
+                    for (int u = 0; u < kUR; ++u)
+                        if (i0 + u * blockDim.x < v_hi) o[u] = MmReduce<T>::ld(c.stage_mc + in_off + ((i0 + u * blockDim.x) << 4));
+#pragma unroll
+                    for (int u = 0; u < kUR; ++u)
+                        if (i0 + u * blockDim.x < v_hi) store_result_vec<T>(dst, extra, i0 + u * blockDim.x, o[u], dv);
+                }
+            }
+            row_barrier(c, bank, blockIdx.x, epoch + 1);   // nobody repacks this staging region before the root is done
+            return;
+        }
+    }
     // my share of the CTA range
     const int64_t share = (cnt + c.world - 1) / c.world;
     const int64_t s_lo = std::min<int64_t>(v_lo + c.rank * share, v_hi);
@@ -300,11 +520,20 @@ allreduce_twoshot_kernel(CommDev c, const T* __restrict__ src, T* __restrict__ d
 #pragma unroll
             for (int u = 0; u < kU; ++u)
                 if (i0 + u * blockDim.x < s_hi) o[u] = MmReduce<T>::ld(c.stage_mc + in_off + ((i0 + u * blockDim.x) << 4));
+        } else {
+            reduce_batch<T, OP>(c, in_off, i0, blockDim.x, s_hi, o);
+        }
+        if (root >= 0) {
+            // reduce-to-root: every rank still reduces its share (the load is spread), only the root receives it
+            char* qp = c.stage[root] + out_off;
+#pragma unroll
+            for (int u = 0; u < kU; ++u)
+                if (i0 + u * blockDim.x < s_hi) st_v4(qp + ((i0 + u * blockDim.x) << 4), o[u]);
+        } else if constexpr (NVLS && MmReduce<T>::ok) {
 #pragma unroll
             for (int u = 0; u < kU; ++u)
                 if (i0 + u * blockDim.x < s_hi) mm_st_v4(c.stage_mc + out_off + ((i0 + u * blockDim.x) << 4), o[u]);
         } else {
-            reduce_batch<T, OP>(c, in_off, i0, blockDim.x, s_hi, o);
 #pragma unroll 1
             for (int p = 0; p < c.world; ++p) {
                 const int q = (c.rank + p) % c.world;  // spread the store targets over the links
@@ -316,6 +545,7 @@ allreduce_twoshot_kernel(CommDev c, const T* __restrict__ src, T* __restrict__ d
         }
     }
     row_barrier(c, bank, blockIdx.x, epoch + 1);
+    if (root >= 0 && c.rank != root) return;
     const uint4* my_out = reinterpret_cast<const uint4*>(c.stage[c.rank] + out_off);
     const bool dst_vec = (reinterpret_cast<uintptr_t>(dst) & 15) == 0 &&
                          (extra == nullptr || (reinterpret_cast<uintptr_t>(extra) & 15) == 0);
@@ -543,27 +773,41 @@ static size_t dtype_size(int dt) {
     return 0;
 }
 
+// CTAs of a zero-copy kernel: these only run for large messages, so take the full channel count.
+static int direct_ctas(const dlbb_comm* c) { return c->ctas > 0 ? std::min(c->ctas, kMaxCtas) : 128; }
+
 template <typename T, int OP>
 static int launch_reduce_T(dlbb_comm* c, const void* src, void* dst, const void* extra, const PieceList& pack,
-                           const ViewDev& view, int64_t red_off, int64_t red_n, int64_t bytes_hint, cudaStream_t s) {
+                           const ViewDev& view, int64_t red_off, int64_t red_n, int64_t bytes_hint, cudaStream_t s,
+                           const PeerView* direct) {
+    if (direct) {
+        const uint32_t ep = c->epoch[0] + 1;
+        c->epoch[0] += 2;
+        reduce_kernel<T, OP><<<direct_ctas(c), kCollThreads, 0, s>>>(
+            c->dev, static_cast<const T*>(src), static_cast<T*>(dst), static_cast<const T*>(extra), pack, view, red_off,
+            red_n, 0, 0, ep, *direct, 1);
+        DLBB_CHECK_LAUNCH("reduce_kernel (zero-copy)");
+        return 0;
+    }
     const int ctas = pick_ctas(c, bytes_hint);
     const int64_t so = next_stage_off(c);
     const uint32_t ep = ++c->epoch[0];
     reduce_kernel<T, OP><<<ctas, kCollThreads, 0, s>>>(c->dev, static_cast<const T*>(src), static_cast<T*>(dst),
                                                        static_cast<const T*>(extra), pack, view, red_off, red_n, so, 0,
-                                                       ep);
+                                                       ep, PeerView{}, 0);
     DLBB_CHECK_LAUNCH("reduce_kernel");
     return 0;
 }
 
 template <typename T>
 static int launch_reduce_op(dlbb_comm* c, int op, const void* src, void* dst, const void* extra, const PieceList& pack,
-                            const ViewDev& view, int64_t red_off, int64_t red_n, int64_t bytes_hint, cudaStream_t s) {
+                            const ViewDev& view, int64_t red_off, int64_t red_n, int64_t bytes_hint, cudaStream_t s,
+                            const PeerView* direct) {
     switch (op) {
-        case DLBB_SUM: return launch_reduce_T<T, DLBB_SUM>(c, src, dst, extra, pack, view, red_off, red_n, bytes_hint, s);
-        case DLBB_MAX: return launch_reduce_T<T, DLBB_MAX>(c, src, dst, extra, pack, view, red_off, red_n, bytes_hint, s);
-        case DLBB_MIN: return launch_reduce_T<T, DLBB_MIN>(c, src, dst, extra, pack, view, red_off, red_n, bytes_hint, s);
-        case DLBB_PROD: return launch_reduce_T<T, DLBB_PROD>(c, src, dst, extra, pack, view, red_off, red_n, bytes_hint, s);
+        case DLBB_SUM: return launch_reduce_T<T, DLBB_SUM>(c, src, dst, extra, pack, view, red_off, red_n, bytes_hint, s, direct);
+        case DLBB_MAX: return launch_reduce_T<T, DLBB_MAX>(c, src, dst, extra, pack, view, red_off, red_n, bytes_hint, s, direct);
+        case DLBB_MIN: return launch_reduce_T<T, DLBB_MIN>(c, src, dst, extra, pack, view, red_off, red_n, bytes_hint, s, direct);
+        case DLBB_PROD: return launch_reduce_T<T, DLBB_PROD>(c, src, dst, extra, pack, view, red_off, red_n, bytes_hint, s, direct);
     }
     set_error("unknown reduce op %d", op);
     return -2;
@@ -571,14 +815,14 @@ static int launch_reduce_op(dlbb_comm* c, int op, const void* src, void* dst, co
 
 static int launch_reduce(dlbb_comm* c, int dtype, int op, const void* src, void* dst, const void* extra,
                          const PieceList& pack, const ViewDev& view, int64_t red_off, int64_t red_n,
-                         int64_t bytes_hint, cudaStream_t s) {
+                         int64_t bytes_hint, cudaStream_t s, const PeerView* direct = nullptr) {
     switch (dtype) {
-        case DLBB_F16: return launch_reduce_op<__half>(c, op, src, dst, extra, pack, view, red_off, red_n, bytes_hint, s);
-        case DLBB_BF16: return launch_reduce_op<__nv_bfloat16>(c, op, src, dst, extra, pack, view, red_off, red_n, bytes_hint, s);
-        case DLBB_F32: return launch_reduce_op<float>(c, op, src, dst, extra, pack, view, red_off, red_n, bytes_hint, s);
-        case DLBB_F64: return launch_reduce_op<double>(c, op, src, dst, extra, pack, view, red_off, red_n, bytes_hint, s);
-        case DLBB_I32: return launch_reduce_op<int32_t>(c, op, src, dst, extra, pack, view, red_off, red_n, bytes_hint, s);
-        case DLBB_I64: return launch_reduce_op<int64_t>(c, op, src, dst, extra, pack, view, red_off, red_n, bytes_hint, s);
+        case DLBB_F16: return launch_reduce_op<__half>(c, op, src, dst, extra, pack, view, red_off, red_n, bytes_hint, s, direct);
+        case DLBB_BF16: return launch_reduce_op<__nv_bfloat16>(c, op, src, dst, extra, pack, view, red_off, red_n, bytes_hint, s, direct);
+        case DLBB_F32: return launch_reduce_op<float>(c, op, src, dst, extra, pack, view, red_off, red_n, bytes_hint, s, direct);
+        case DLBB_F64: return launch_reduce_op<double>(c, op, src, dst, extra, pack, view, red_off, red_n, bytes_hint, s, direct);
+        case DLBB_I32: return launch_reduce_op<int32_t>(c, op, src, dst, extra, pack, view, red_off, red_n, bytes_hint, s, direct);
+        case DLBB_I64: return launch_reduce_op<int64_t>(c, op, src, dst, extra, pack, view, red_off, red_n, bytes_hint, s, direct);
     }
     set_error("reduction on unsupported dtype %d", dtype);
     return -2;
@@ -586,13 +830,13 @@ static int launch_reduce(dlbb_comm* c, int dtype, int op, const void* src, void*
 
 template <typename T, int OP>
 static int launch_twoshot_T(dlbb_comm* c, bool nvls, const void* src, void* dst, const void* extra, const ViewDev& view,
-                            int64_t src_off, int64_t n, cudaStream_t s) {
+                            int64_t src_off, int64_t n, cudaStream_t s, int root) {
     const int64_t bytes = n * (int64_t)sizeof(T);
     const int64_t in_off = next_stage_off(c);
     const int64_t out_off = in_off == 0 ? static_cast<int64_t>(c->stage_bytes) : 0;
     const bool use_nvls = nvls && MmReduce<T>::ok && OP == DLBB_SUM;
     static const int64_t pipe_min = getenv("DLBB_PIPELINE_MIN_BYTES") ? atoll(getenv("DLBB_PIPELINE_MIN_BYTES")) : (8ll << 20);
-    if (bytes >= pipe_min && use_nvls) {
+    if (bytes >= pipe_min && use_nvls && root < 0) {
         // large message on the multicast path: pack / reduce / unpack overlapped inside each CTA
         // (measured at 8 GPUs, 256 MiB: 631 GB/s busbw vs 515 for the phase-by-phase kernel and 646 for NCCL;
         // the peer-load variant does not profit - 362 vs 430 - and keeps the phase-by-phase kernel)
@@ -622,51 +866,108 @@ static int launch_twoshot_T(dlbb_comm* c, bool nvls, const void* src, void* dst,
     if (use_nvls)
         allreduce_twoshot_kernel<T, OP, true><<<ctas, kCollThreads, 0, s>>>(
             c->dev, static_cast<const T*>(src), static_cast<T*>(dst), static_cast<const T*>(extra), view, src_off, n,
-            in_off, out_off, 0, ep);
+            in_off, out_off, 0, ep, root);
     else
         allreduce_twoshot_kernel<T, OP, false><<<ctas, kCollThreads, 0, s>>>(
             c->dev, static_cast<const T*>(src), static_cast<T*>(dst), static_cast<const T*>(extra), view, src_off, n,
-            in_off, out_off, 0, ep);
+            in_off, out_off, 0, ep, root);
     DLBB_CHECK_LAUNCH("allreduce_twoshot_kernel");
     return 0;
 }
 
 template <typename T>
 static int launch_twoshot_op(dlbb_comm* c, int op, bool nvls, const void* src, void* dst, const void* extra,
-                             const ViewDev& view, int64_t src_off, int64_t n, cudaStream_t s) {
+                             const ViewDev& view, int64_t src_off, int64_t n, cudaStream_t s, int root) {
     switch (op) {
-        case DLBB_SUM: return launch_twoshot_T<T, DLBB_SUM>(c, nvls, src, dst, extra, view, src_off, n, s);
-        case DLBB_MAX: return launch_twoshot_T<T, DLBB_MAX>(c, false, src, dst, extra, view, src_off, n, s);
-        case DLBB_MIN: return launch_twoshot_T<T, DLBB_MIN>(c, false, src, dst, extra, view, src_off, n, s);
-        case DLBB_PROD: return launch_twoshot_T<T, DLBB_PROD>(c, false, src, dst, extra, view, src_off, n, s);
+        case DLBB_SUM: return launch_twoshot_T<T, DLBB_SUM>(c, nvls, src, dst, extra, view, src_off, n, s, root);
+        case DLBB_MAX: return launch_twoshot_T<T, DLBB_MAX>(c, false, src, dst, extra, view, src_off, n, s, root);
+        case DLBB_MIN: return launch_twoshot_T<T, DLBB_MIN>(c, false, src, dst, extra, view, src_off, n, s, root);
+        case DLBB_PROD: return launch_twoshot_T<T, DLBB_PROD>(c, false, src, dst, extra, view, src_off, n, s, root);
     }
     set_error("unknown reduce op %d", op);
     return -2;
 }
 
+// root < 0: all-reduce; root >= 0: reduce to that rank (same data flow, only the root receives and unpacks)
 static int launch_twoshot(dlbb_comm* c, int dtype, int op, bool nvls, const void* src, void* dst, const void* extra,
-                          const ViewDev& view, int64_t src_off, int64_t n, cudaStream_t s) {
+                          const ViewDev& view, int64_t src_off, int64_t n, cudaStream_t s, int root = -1) {
     switch (dtype) {
-        case DLBB_F16: return launch_twoshot_op<__half>(c, op, nvls, src, dst, extra, view, src_off, n, s);
-        case DLBB_BF16: return launch_twoshot_op<__nv_bfloat16>(c, op, nvls, src, dst, extra, view, src_off, n, s);
-        case DLBB_F32: return launch_twoshot_op<float>(c, op, nvls, src, dst, extra, view, src_off, n, s);
-        case DLBB_F64: return launch_twoshot_op<double>(c, op, false, src, dst, extra, view, src_off, n, s);
-        case DLBB_I32: return launch_twoshot_op<int32_t>(c, op, false, src, dst, extra, view, src_off, n, s);
-        case DLBB_I64: return launch_twoshot_op<int64_t>(c, op, false, src, dst, extra, view, src_off, n, s);
+        case DLBB_F16: return launch_twoshot_op<__half>(c, op, nvls, src, dst, extra, view, src_off, n, s, root);
+        case DLBB_BF16: return launch_twoshot_op<__nv_bfloat16>(c, op, nvls, src, dst, extra, view, src_off, n, s, root);
+        case DLBB_F32: return launch_twoshot_op<float>(c, op, nvls, src, dst, extra, view, src_off, n, s, root);
+        case DLBB_F64: return launch_twoshot_op<double>(c, op, false, src, dst, extra, view, src_off, n, s, root);
+        case DLBB_I32: return launch_twoshot_op<int32_t>(c, op, false, src, dst, extra, view, src_off, n, s, root);
+        case DLBB_I64: return launch_twoshot_op<int64_t>(c, op, false, src, dst, extra, view, src_off, n, s, root);
     }
     set_error("reduction on unsupported dtype %d", dtype);
     return -2;
 }
 
 static int launch_move(dlbb_comm* c, const void* src, void* dst, const PieceList& pack, const PieceList& pull,
-                       const ViewDev& view, int elem_size, int64_t bytes_hint, cudaStream_t s) {
+                       const ViewDev& view, int elem_size, int64_t bytes_hint, cudaStream_t s,
+                       const PeerView* direct = nullptr) {
+    if (direct) {
+        const uint32_t ep = c->epoch[0] + 1;
+        c->epoch[0] += 2;
+        move_kernel<<<direct_ctas(c), kCollThreads, 0, s>>>(c->dev, static_cast<const char*>(src), static_cast<char*>(dst),
+                                                            pack, pull, view, elem_size, 0, 0, ep, *direct, 1);
+        DLBB_CHECK_LAUNCH("move_kernel (zero-copy)");
+        return 0;
+    }
     const int ctas = pick_ctas(c, bytes_hint);
     const int64_t so = next_stage_off(c);
     const uint32_t ep = ++c->epoch[0];
     move_kernel<<<ctas, kCollThreads, 0, s>>>(c->dev, static_cast<const char*>(src), static_cast<char*>(dst), pack, pull,
-                                              view, elem_size, so, 0, ep);
+                                              view, elem_size, so, 0, ep, PeerView{}, 0);
     DLBB_CHECK_LAUNCH("move_kernel");
     return 0;
+}
+
+// Zero-copy gate shared by every collective: large enough, enabled, and every rank's buffer exportable.
+// Collective and host-blocking when it goes as far as the exchange (see peer_registry.cpp).
+static int try_zero_copy(dlbb_comm* c, const void* buf, int64_t bytes, int64_t gate_bytes, PeerView* pv, bool* ok) {
+    *ok = false;
+    if (c->world == 1 || c->zero_copy_min == 0 || gate_bytes < (int64_t)c->zero_copy_min) return 0;
+    return peer_registry_resolve(c, c->reg, buf, static_cast<size_t>(bytes), pv, ok);
+}
+
+static bool disjoint(const void* a, int64_t an, const void* b, int64_t bn) {
+    const char* pa = static_cast<const char*>(a);
+    const char* pb = static_cast<const char*>(b);
+    return pa + an <= pb || pb + bn <= pa;
+}
+static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+
+template <typename T, int OP>
+static int launch_allreduce_direct_T(dlbb_comm* c, const PeerView& pv, int64_t n, cudaStream_t s) {
+    const uint32_t ep = c->epoch[0] + 1;
+    c->epoch[0] += 2;
+    allreduce_direct_kernel<T, OP><<<direct_ctas(c), kCollThreads, 0, s>>>(c->dev, pv, n, 0, ep);
+    DLBB_CHECK_LAUNCH("allreduce_direct_kernel");
+    return 0;
+}
+template <typename T>
+static int launch_allreduce_direct_op(dlbb_comm* c, int op, const PeerView& pv, int64_t n, cudaStream_t s) {
+    switch (op) {
+        case DLBB_SUM: return launch_allreduce_direct_T<T, DLBB_SUM>(c, pv, n, s);
+        case DLBB_MAX: return launch_allreduce_direct_T<T, DLBB_MAX>(c, pv, n, s);
+        case DLBB_MIN: return launch_allreduce_direct_T<T, DLBB_MIN>(c, pv, n, s);
+        case DLBB_PROD: return launch_allreduce_direct_T<T, DLBB_PROD>(c, pv, n, s);
+    }
+    set_error("unknown reduce op %d", op);
+    return -2;
+}
+static int launch_allreduce_direct(dlbb_comm* c, int dtype, int op, const PeerView& pv, int64_t n, cudaStream_t s) {
+    switch (dtype) {
+        case DLBB_F16: return launch_allreduce_direct_op<__half>(c, op, pv, n, s);
+        case DLBB_BF16: return launch_allreduce_direct_op<__nv_bfloat16>(c, op, pv, n, s);
+        case DLBB_F32: return launch_allreduce_direct_op<float>(c, op, pv, n, s);
+        case DLBB_F64: return launch_allreduce_direct_op<double>(c, op, pv, n, s);
+        case DLBB_I32: return launch_allreduce_direct_op<int32_t>(c, op, pv, n, s);
+        case DLBB_I64: return launch_allreduce_direct_op<int64_t>(c, op, pv, n, s);
+    }
+    set_error("reduction on unsupported dtype %d", dtype);
+    return -2;
 }
 
 static int allreduce_impl(dlbb_comm* c, const void* in, void* out, const void* extra, int64_t count, int dtype, int op,
@@ -677,6 +978,8 @@ static int allreduce_impl(dlbb_comm* c, const void* in, void* out, const void* e
     if (count == 0) return 0;
     const ViewDev view = make_view(in_view);
     if (algo == DLBB_ALGO_AUTO) algo = c->default_algo;
+    const bool force_direct = algo == DLBB_ALGO_DIRECT;
+    if (force_direct) algo = DLBB_ALGO_AUTO;   // for whatever cannot go zero-copy
     const int64_t VE = 16 / (int64_t)es;
     const int64_t cap = static_cast<int64_t>(c->stage_bytes / es) / (VE * c->world) * (VE * c->world);
     const bool nvls_ok = dlbb_comm_has_multicast(c) && op == DLBB_SUM && (dtype == DLBB_F16 || dtype == DLBB_BF16 || dtype == DLBB_F32);
@@ -686,6 +989,26 @@ static int allreduce_impl(dlbb_comm* c, const void* in, void* out, const void* e
     int64_t oneshot_max = c->oneshot_max ? (int64_t)c->oneshot_max
                         : (c->world <= 2 ? INT64_MAX : (nvls_ok && algo == DLBB_ALGO_AUTO ? 0 : (512 << 10)));
     int64_t done = 0;
+    // Zero-copy: in place on contiguous plain allocations, at most one NVSwitch domain (8 ranks).  The part that is
+    // a multiple of 16 B x world goes direct, a ragged tail (if any) through the staged kernels below.
+    // (Conditions that may differ between ranks - out of place, misaligned - are folded into the exchange as a
+    // null buffer so that every rank still takes part in it and all of them fall back together.)
+    if (extra == nullptr && view.ndim == 0 && c->world <= kDirectMaxWorld && algo == DLBB_ALGO_AUTO) {
+        PeerView pv;
+        bool zc = false;
+        const int64_t gate = force_direct ? INT64_MAX : count * (int64_t)es;
+        const bool mine_ok = in == out && (reinterpret_cast<uintptr_t>(out) & 15) == 0;
+        const int rc = try_zero_copy(c, mine_ok ? out : nullptr, count * (int64_t)es, gate, &pv, &zc);
+        if (rc) return rc;
+        if (zc) {
+            const int64_t n = count / (VE * c->world) * (VE * c->world);
+            if (n > 0) {
+                const int rc2 = launch_allreduce_direct(c, dtype, op, pv, n, s);
+                if (rc2) return rc2;
+                done = n;
+            }
+        }
+    }
     while (done < count) {
         const int64_t left = count - done;
         const int64_t bytes = left * (int64_t)es;
@@ -742,6 +1065,44 @@ int dlbb_reduce(dlbb_comm_t* c, const void* in, void* out, int64_t count, int dt
     const size_t es = dtype_size(dtype);
     DLBB_REQUIRE(es != 0 && dtype != DLBB_U8, "reduce: unsupported dtype %d", dtype);
     DLBB_REQUIRE(root >= 0 && root < c->world, "reduce: bad root %d", root);
+    const int64_t VE = 16 / (int64_t)es;
+    const bool nvls_ok = dlbb_comm_has_multicast(c) && op == DLBB_SUM &&
+                         (dtype == DLBB_F16 || dtype == DLBB_BF16 || dtype == DLBB_F32);
+    if (c->world > 2 && (nvls_ok || count * (int64_t)es > (512 << 10))) {
+        // More than one sender: a root that pulls everything is limited by its own link ((world-1) x the message;
+        // measured at 8 GPUs, 128 MiB: 109 GB/s).  Use the all-reduce data flow instead - every rank reduces
+        // 1/world of the message (in the switch when NVLS applies) - and deliver the shares to the root only.
+        const int64_t unit = VE * c->world;
+        const int64_t cap2 = static_cast<int64_t>(c->stage_bytes / es) / unit * unit;
+        int64_t done = 0;
+        while (count - done >= unit) {
+            const int64_t n = std::min(count - done, cap2) / unit * unit;
+            const int rc = launch_twoshot(c, dtype, op, nvls_ok, in, static_cast<char*>(out) + done * es, nullptr, ViewDev{},
+                                          done, n, static_cast<cudaStream_t>(stream), root);
+            if (rc) return rc;
+            done += n;
+        }
+        if (done < count) {   // ragged tail: single-barrier form
+            const int64_t n = count - done;
+            PieceList pack{};
+            pack.count = 1;
+            pack.p[0] = Piece{0, done, 0, n};
+            const int rc = launch_reduce(c, dtype, op, in, static_cast<char*>(out) + done * es, nullptr, pack, ViewDev{}, 0,
+                                         c->rank == root ? n : 0, n * es, static_cast<cudaStream_t>(stream));
+            if (rc) return rc;
+        }
+        return 0;
+    }
+    {   // zero-copy (two ranks): the root reduces straight out of the peer's input tensor
+        PeerView pv;
+        bool zc = false;
+        const bool mine_ok = aligned16(in) && (c->rank != root || aligned16(out));
+        const int rc = try_zero_copy(c, mine_ok ? in : nullptr, count * (int64_t)es, count * (int64_t)es, &pv, &zc);
+        if (rc) return rc;
+        if (zc)
+            return launch_reduce(c, dtype, op, in, out, nullptr, PieceList{}, ViewDev{}, 0, c->rank == root ? count : 0,
+                                 count * es, static_cast<cudaStream_t>(stream), &pv);
+    }
     const int64_t cap = static_cast<int64_t>(c->stage_bytes / es);
     for (int64_t done = 0; done < count; done += cap) {
         const int64_t n = std::min(cap, count - done);
@@ -758,6 +1119,17 @@ int dlbb_reduce(dlbb_comm_t* c, const void* in, void* out, int64_t count, int dt
 int dlbb_reduce_scatter(dlbb_comm_t* c, const void* in, void* out, int64_t cpr, int dtype, int op, void* stream) {
     const size_t es = dtype_size(dtype);
     DLBB_REQUIRE(es != 0 && dtype != DLBB_U8, "reduce_scatter: unsupported dtype %d", dtype);
+    if ((cpr * (int64_t)es) % 16 == 0) {   // zero-copy: rank r reduces shard r of every rank's input tensor
+        PeerView pv;
+        bool zc = false;
+        const int64_t total = cpr * (int64_t)es * c->world;
+        const bool mine_ok = aligned16(in) && aligned16(out);
+        const int rc = try_zero_copy(c, mine_ok ? in : nullptr, total, total, &pv, &zc);
+        if (rc) return rc;
+        if (zc)
+            return launch_reduce(c, dtype, op, in, out, nullptr, PieceList{}, ViewDev{}, c->rank * cpr, cpr, total,
+                                 static_cast<cudaStream_t>(stream), &pv);
+    }
     // per launch every rank stages `chunk` elements for each destination rank
     int64_t cap = static_cast<int64_t>(c->stage_bytes / es) / c->world;
     cap = cap / 16 * 16;
@@ -782,6 +1154,24 @@ int dlbb_allgather(dlbb_comm_t* c, const void* in, void* out, int64_t cpr, int d
     const int64_t total = cpr * es;
     const int64_t cap = static_cast<int64_t>(c->stage_bytes) / 64 * 64;
     const ViewDev view = make_view(in_view);
+    if (view.ndim == 0) {   // zero-copy: pull every rank's input tensor straight into my output
+        PeerView pv;
+        bool zc = false;
+        char* my_slot = static_cast<char*>(out) + c->rank * total;
+        const bool mine_ok = in == my_slot || disjoint(in, total, out, total * c->world);
+        const int rc = try_zero_copy(c, mine_ok ? in : nullptr, total, total * c->world, &pv, &zc);
+        if (rc) return rc;
+        if (zc) {
+            PieceList pull{};
+            pull.count = c->world;
+            for (int i = 0; i < c->world; ++i) {
+                const int p = (c->rank + i) % c->world;
+                pull.p[i] = Piece{p, 0, p * total, total};
+            }
+            return launch_move(c, in, out, PieceList{}, pull, view, (int)es, total * c->world,
+                               static_cast<cudaStream_t>(stream), &pv);
+        }
+    }
     for (int64_t done = 0; done < total; done += cap) {
         const int64_t n = std::min(cap, total - done);
         PieceList pack{}, pull{};
@@ -803,6 +1193,37 @@ int dlbb_broadcast(dlbb_comm_t* c, void* buf, int64_t count, int dtype, int root
     DLBB_REQUIRE(es != 0, "broadcast: unsupported dtype %d", dtype);
     DLBB_REQUIRE(root >= 0 && root < c->world, "broadcast: bad root %d", root);
     const int64_t total = count * es, cap = static_cast<int64_t>(c->stage_bytes) / 64 * 64;
+    if (c->world > 2 && dlbb_comm_has_multicast(c)) {
+        // More than one receiver: one multicast store through the switch instead of world-1 pulls from the root
+        // (measured at 8 GPUs, 128 MiB: 109 GB/s for the pull forms - the root's link carries the message 7 times).
+        for (int64_t done = 0; done < total; done += cap) {
+            const int64_t n = std::min(cap, total - done);
+            const int ctas = c->ctas > 0 ? std::min(c->ctas, kMaxCtas)
+                                         : static_cast<int>(std::min<int64_t>(128, std::max<int64_t>(1, n / (64 << 10))));
+            const int64_t so = next_stage_off(c);
+            const int64_t per = ((n >> 4) + ctas - 1) / ctas;
+            const int nchunks = static_cast<int>(std::max<int64_t>(1, (per + kBcChunkVecs - 1) / kBcChunkVecs));
+            const uint32_t fb = c->epoch[kBcFlagBank];
+            c->epoch[kBcFlagBank] += nchunks;
+            const uint32_t ep = ++c->epoch[0];
+            broadcast_nvls_kernel<<<ctas, kCollThreads, 0, static_cast<cudaStream_t>(stream)>>>(
+                c->dev, static_cast<const char*>(buf) + done, static_cast<char*>(buf) + done, n, root, so, fb, nchunks, 0, ep);
+            DLBB_CHECK_LAUNCH("broadcast_nvls_kernel");
+        }
+        return 0;
+    }
+    {   // zero-copy: everyone pulls from the root's tensor
+        PeerView pv;
+        bool zc = false;
+        const int rc = try_zero_copy(c, buf, total, total, &pv, &zc);
+        if (rc) return rc;
+        if (zc) {
+            PieceList pull{};
+            if (c->rank != root) { pull.count = 1; pull.p[0] = Piece{root, 0, 0, total}; }
+            return launch_move(c, buf, buf, PieceList{}, pull, ViewDev{}, (int)es, total, static_cast<cudaStream_t>(stream),
+                               &pv);
+        }
+    }
     for (int64_t done = 0; done < total; done += cap) {
         const int64_t n = std::min(cap, total - done);
         PieceList pack{}, pull{};
@@ -819,6 +1240,23 @@ int dlbb_gather(dlbb_comm_t* c, const void* in, void* out, int64_t count, int dt
     DLBB_REQUIRE(es != 0, "gather: unsupported dtype %d", dtype);
     DLBB_REQUIRE(root >= 0 && root < c->world, "gather: bad root %d", root);
     const int64_t total = count * es, cap = static_cast<int64_t>(c->stage_bytes) / 64 * 64;
+    {   // zero-copy: the root pulls every rank's input tensor
+        PeerView pv;
+        bool zc = false;
+        const bool mine_ok = c->rank != root || in == static_cast<char*>(out) + root * total ||
+                             disjoint(in, total, out, total * c->world);
+        const int rc = try_zero_copy(c, mine_ok ? in : nullptr, total, total * c->world, &pv, &zc);
+        if (rc) return rc;
+        if (zc) {
+            PieceList pull{};
+            if (c->rank == root) {
+                pull.count = c->world;
+                for (int p = 0; p < c->world; ++p) pull.p[p] = Piece{p, 0, p * total, total};
+            }
+            return launch_move(c, in, out, PieceList{}, pull, ViewDev{}, (int)es, total * c->world,
+                               static_cast<cudaStream_t>(stream), &pv);
+        }
+    }
     for (int64_t done = 0; done < total; done += cap) {
         const int64_t n = std::min(cap, total - done);
         PieceList pack{}, pull{};
@@ -839,6 +1277,23 @@ int dlbb_scatter(dlbb_comm_t* c, const void* in, void* out, int64_t count, int d
     DLBB_REQUIRE(es != 0, "scatter: unsupported dtype %d", dtype);
     DLBB_REQUIRE(root >= 0 && root < c->world, "scatter: bad root %d", root);
     const int64_t total = count * es;
+    {   // zero-copy: everyone pulls its slice of the root's tensor (non-roots export their output as a stand-in)
+        PeerView pv;
+        bool zc = false;
+        const bool is_root = c->rank == root;
+        const bool mine_ok = !is_root || (in != nullptr && disjoint(in, total * c->world, out, total));
+        const void* mine = is_root ? in : out;
+        const int rc = try_zero_copy(c, mine_ok ? mine : nullptr, is_root ? total * c->world : total, total * c->world,
+                                     &pv, &zc);
+        if (rc) return rc;
+        if (zc) {
+            PieceList pull{};
+            pull.count = 1;
+            pull.p[0] = Piece{root, c->rank * total, 0, total};
+            return launch_move(c, in, out, PieceList{}, pull, ViewDev{}, (int)es, total * c->world,
+                               static_cast<cudaStream_t>(stream), &pv);
+        }
+    }
     const int64_t cap = static_cast<int64_t>(c->stage_bytes) / c->world / 64 * 64;
     DLBB_REQUIRE(cap > 0, "scatter: staging too small");
     for (int64_t done = 0; done < total; done += cap) {
@@ -861,6 +1316,23 @@ int dlbb_alltoall(dlbb_comm_t* c, const void* in, void* out, int64_t cpr, int dt
     const int64_t es = (int64_t)dtype_size(dtype);
     DLBB_REQUIRE(es != 0, "alltoall: unsupported dtype %d", dtype);
     const int64_t total = cpr * es;
+    {   // zero-copy: pull my slice out of every rank's input tensor
+        PeerView pv;
+        bool zc = false;
+        const bool mine_ok = disjoint(in, total * c->world, out, total * c->world);
+        const int rc = try_zero_copy(c, mine_ok ? in : nullptr, total * c->world, total * c->world, &pv, &zc);
+        if (rc) return rc;
+        if (zc) {
+            PieceList pull{};
+            pull.count = c->world;
+            for (int i = 0; i < c->world; ++i) {
+                const int p = (c->rank + i) % c->world;
+                pull.p[i] = Piece{p, c->rank * total, p * total, total};
+            }
+            return launch_move(c, in, out, PieceList{}, pull, ViewDev{}, (int)es, total * c->world,
+                               static_cast<cudaStream_t>(stream), &pv);
+        }
+    }
     const int64_t cap = static_cast<int64_t>(c->stage_bytes) / c->world / 64 * 64;
     DLBB_REQUIRE(cap > 0, "alltoall: staging too small");
     for (int64_t done = 0; done < total; done += cap) {

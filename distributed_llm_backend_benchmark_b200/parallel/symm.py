@@ -20,7 +20,7 @@ VP, I, I64, F, SZ = C.c_void_p, C.c_int, C.c_int64, C.c_float, C.c_size_t
 DTYPES = {torch.float16: 0, torch.bfloat16: 1, torch.float32: 2, torch.float64: 3, torch.uint8: 4, torch.int8: 4,
           torch.int32: 5, torch.int64: 6}
 OPS = {"sum": 0, "max": 1, "min": 2, "prod": 3}
-ALGOS = {"auto": 0, "oneshot": 1, "twoshot": 2, "nvls": 3}
+ALGOS = {"auto": 0, "oneshot": 1, "twoshot": 2, "nvls": 3, "direct": 4}
 
 
 class _View(C.Structure):
@@ -40,6 +40,8 @@ _SIGS = {
     "dlbb_symm_free": (I, [VP, I]),
     "dlbb_comm_set_ctas": (None, [VP, I]),
     "dlbb_comm_set_oneshot_max_bytes": (None, [VP, SZ]),
+    "dlbb_comm_set_zero_copy_min_bytes": (None, [VP, SZ]),
+    "dlbb_comm_zero_copy_min_bytes": (SZ, [VP]),
     "dlbb_barrier": (I, [VP, VP]),
     "dlbb_allreduce": (I, [VP, VP, VP, I64, I, I, I, C.POINTER(_View), VP]),
     "dlbb_allreduce_residual_bf16": (I, [VP, VP, VP, VP, I64, VP]),
@@ -142,6 +144,17 @@ class SymmComm:
 
     def set_oneshot_max_bytes(self, n: int) -> None:
         self.lib.dlbb_comm_set_oneshot_max_bytes(self.h, n)
+
+    def set_zero_copy_min_bytes(self, n: int) -> None:
+        """Messages of at least `n` bytes on plain (cudaMalloc / caching-allocator) tensors are exchanged directly
+        between the ranks' own tensors instead of through the staging area (0 = never).  Must be set to the same
+        value on every rank; such a call blocks the host until every rank has issued it."""
+        self.lib.dlbb_comm_set_zero_copy_min_bytes(self.h, n)
+
+    @property
+    def zero_copy_min_bytes(self) -> int:
+        """0 when zero-copy is unavailable (single rank, IPC self-test failed) or switched off."""
+        return int(self.lib.dlbb_comm_zero_copy_min_bytes(self.h))
 
     # ------------------------------------------------------------------ symmetric tensors
     def alloc(self, numel: int, dtype: torch.dtype = torch.bfloat16) -> tuple[torch.Tensor, int]:

@@ -29,7 +29,8 @@ typedef struct dlbb_comm dlbb_comm_t;
 
 enum { DLBB_SUM = 0, DLBB_MAX = 1, DLBB_MIN = 2, DLBB_PROD = 3 };
 /* all-reduce algorithms (the analogue of oneCCL's CCL_ALLREDUCE, collectives/3d/launch_dsccl.sh:46) */
-enum { DLBB_ALGO_AUTO = 0, DLBB_ALGO_ONESHOT = 1, DLBB_ALGO_TWOSHOT = 2, DLBB_ALGO_NVLS = 3 };
+enum { DLBB_ALGO_AUTO = 0, DLBB_ALGO_ONESHOT = 1, DLBB_ALGO_TWOSHOT = 2, DLBB_ALGO_NVLS = 3,
+       DLBB_ALGO_DIRECT = 4 /* zero-copy on the ranks' own tensors at any size (in place only; else falls back) */ };
 
 /* Create a communicator.  `job` names the rendezvous (all ranks pass the same string, e.g.
  * "<MASTER_PORT>-<sequence>"); `device` is the CUDA ordinal this rank drives.  Collective call:
@@ -60,6 +61,14 @@ int dlbb_symm_free(dlbb_comm_t* c, int seg_id);
  * ctas: number of CTAs ("channels") a collective kernel uses, 0 = auto. */
 void dlbb_comm_set_ctas(dlbb_comm_t* c, int ctas);
 void dlbb_comm_set_oneshot_max_bytes(dlbb_comm_t* c, size_t bytes);
+/* Zero-copy collectives: messages of at least `bytes` bytes whose tensors are plain cudaMalloc memory (e.g. the
+ * PyTorch caching allocator) are read from / written to the peers' tensors directly instead of going through the
+ * symmetric staging area (CUDA IPC mappings, cached; all-reduce in place, all-gather, broadcast, gather, scatter,
+ * all-to-all, reduce, reduce-scatter).  Such a call blocks the calling host thread until every rank has issued the
+ * same call (a shared-memory mailbox exchange, ~1 us when the peers are there).  0 disables; default 16 MiB
+ * (env DLBB_ZEROCOPY_MIN_BYTES).  No counterpart in the reference. */
+void dlbb_comm_set_zero_copy_min_bytes(dlbb_comm_t* c, size_t bytes);
+size_t dlbb_comm_zero_copy_min_bytes(const dlbb_comm_t* c);
 
 /* Device barrier across all ranks, enqueued on `stream` (K1; ref comm.Barrier run_mpi.py:177). */
 int dlbb_barrier(dlbb_comm_t* c, void* stream);

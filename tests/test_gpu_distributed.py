@@ -32,6 +32,17 @@ def test_comm_selfcheck(native_lib):
     assert r.returncode == 0 and "COMM ALL OK" in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]
 
 
+def test_zero_copy_collectives(native_lib):
+    """Every collective directly on the ranks' own tensors (CUDA IPC mappings, csrc/bootstrap/peer_registry.cpp),
+    forced at all sizes, against locally computed expectations."""
+    n = nranks()
+    if n < 2:
+        pytest.skip("zero-copy collectives need two GPUs")
+    r = run([BIN / "mpirun", "-np", n, sys.executable, ROOT / "tools" / "gpu_zero_copy.py"],
+            env={"DLBB_SKIP_PERF": "1", "MASTER_PORT": "29633"})
+    assert r.returncode == 0 and "ZERO-COPY CHECK OK" in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]
+
+
 @pytest.mark.parametrize("script", ["test_open.py", "test_deepseed.py", "ccl.py", "test_ccl_backend.py"])
 def test_smoke_scripts_on_native_backend(native_lib, script):
     r = run([BIN / "mpirun", "-n", nranks(), sys.executable, ROOT / "test" / script], env={"DLBB_LOG_LEVEL": "info"})

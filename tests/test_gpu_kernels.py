@@ -33,6 +33,27 @@ def test_gemm_layouts(native_lib, ta, tb, bn):
         native_lib.dlbb_gemm_set_tile_n(0)
 
 
+@pytest.mark.parametrize("ta", [False, True])
+@pytest.mark.parametrize("tb", [False, True])
+@pytest.mark.parametrize("shape", [(512, 768, 320), (300, 520, 200), (4096, 1024, 512)])
+def test_gemm_cta_pair_matches_one_cta_bitwise(native_lib, ta, tb, shape):
+    """The 256 x 256 CTA-pair kernel (tcgen05.mma.cta_group::2, the default) accumulates in the same k order
+    as the one-CTA kernel, so the two must agree bit for bit - also where the pair's second CTA hangs over
+    the matrix edge."""
+    M, N, K = shape
+    a, b = _mk((K, M) if ta else (M, K), pad=8), _mk((N, K) if tb else (K, N), scale=0.5)
+    ref = (a.t() if ta else a).float() @ (b.t() if tb else b).float()
+    outs = []
+    try:
+        for mode in (1, 0):
+            native_lib.dlbb_gemm_set_pair_mode(mode)
+            outs.append(ops.matmul(a, b, transpose_a=ta, transpose_b=tb))
+    finally:
+        native_lib.dlbb_gemm_set_pair_mode(-1)
+    assert relerr(outs[0], ref) < 6e-3
+    assert torch.equal(outs[0], outs[1])
+
+
 @pytest.mark.parametrize("epi", ["gelu", "add", "mul_dgelu"])
 @pytest.mark.parametrize("shape", [(256, 512, 192), (200, 136, 72), (1024, 4096, 1024)])
 def test_gemm_epilogues(native_lib, epi, shape):
