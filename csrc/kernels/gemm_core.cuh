@@ -360,6 +360,19 @@ gemm_bf16_tcgen05_pair_kernel(const __grid_constant__ CUtensorMap tmA,
     gemm_cta_body<256, A_MN, B_MN, NoFusion, 2>(tmA, tmB, tmC, tmAux, p, nf);
 }
 
+// The same kernel capped at 168 registers per thread, for steps that run a second kernel next to the GEMM on the same
+// SMs (the data-parallel bucket kernel): the launch of the uncapped cluster kernel allocates 230 registers per thread
+// (ncu: launch__registers_per_thread) and leaves no room for a co-resident CTA.
+template <bool A_MN, bool B_MN>
+__global__ void __cluster_dims__(2, 1, 1) __maxnreg__(168)
+gemm_bf16_tcgen05_pair_lowreg_kernel(const __grid_constant__ CUtensorMap tmA,
+                              const __grid_constant__ CUtensorMap tmB,
+                              const __grid_constant__ CUtensorMap tmC,
+                              const __grid_constant__ CUtensorMap tmAux, const GemmParams p) {
+    NoFusion nf;
+    gemm_cta_body<256, A_MN, B_MN, NoFusion, 2>(tmA, tmB, tmC, tmAux, p, nf);
+}
+
 // ------------------------------------------------------------------------------------------
 // Host side: cached TMA tensor maps
 // ------------------------------------------------------------------------------------------

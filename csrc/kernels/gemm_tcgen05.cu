@@ -10,6 +10,10 @@
 // and runs its own epilogue.  Shared-memory traffic per MMA drops by a third, which is what limited the
 // one-CTA 128 x 256 kernel; measured 4-14% faster on the 7B model's shapes (profiles/gemm_shapes.md).
 // The one-CTA kernel (below) remains for narrow outputs, DLBB_GEMM_PAIR=0 and the fused GEMM+all-reduce.
+// The default is the pair kernel built with __maxnreg__(168): a cluster launch of the 198-register build allocates
+// 230 registers per thread (ncu launch__registers_per_thread), which keeps the data-parallel bucket kernel
+// (128 threads x 112 registers) off the GEMM's SMs; capped, both fit (200 x 256 + 112 x 128 = 65536) and the
+// 2-GPU training step drops from 156.7 to 145.1 ms (one-CTA kernel: 160.8 ms; profiles/raw/dp_pairmode_n2.json).
 //
 // One CTA per SM, 8 warps: warp 0 = TMA producer, warp 1 = MMA issuer, warp 2 = TMEM
 // allocator, warp 3 idle, warps 4-7 = epilogue (one TMEM lane quarter each).  The accumulator
@@ -29,14 +33,15 @@ namespace dlbb {
 // ------------------------------------------------------------------------------------------
 static int g_force_bn = 0;
 static int g_num_sms = 0;
-static int g_pair_mode = -1;   // -1: from DLBB_GEMM_PAIR (default on), 0: one CTA per tile, 1: CTA pairs
+static int g_pair_mode = -1;   // -1: from DLBB_GEMM_PAIR (default 2), 0: one CTA per tile, 1: CTA pairs,
+                               // 2: CTA pairs capped at 168 registers (leaves room for a co-resident kernel)
 static int g_pair_clusters = 0;
 
-template <bool A_MN, bool B_MN>
+template <bool A_MN, bool B_MN, bool LOWREG>
 static int launch_gemm_pair(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmC,
                             const CUtensorMap& tmAux, const GemmParams& p, int clusters, cudaStream_t stream) {
     using Cfg = GemmCfg<256, 2>;
-    auto kern = gemm_bf16_tcgen05_pair_kernel<A_MN, B_MN>;
+    auto kern = LOWREG ? gemm_bf16_tcgen05_pair_lowreg_kernel<A_MN, B_MN> : gemm_bf16_tcgen05_pair_kernel<A_MN, B_MN>;
     static bool configured = false;
     if (!configured) {
         DLBB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -50,6 +55,7 @@ static int launch_gemm_pair(const CUtensorMap& tmA, const CUtensorMap& tmB, cons
 
 // 256 x 256 tiles on CTA pairs (tcgen05.mma.cta_group::2): each SM stages half of B, so shared-memory
 // traffic per MMA drops by a third against the one-CTA 128 x 256 tile.
+template <bool LOWREG>
 static int dispatch_gemm_pair(const void* A, const void* B, void* C, int M, int N, int K, int64_t lda,
                               int64_t ldb, int64_t ldc, int a_mn, int b_mn, int epi, void* aux,
                               int64_t ld_aux, cudaStream_t stream) {
@@ -85,10 +91,10 @@ static int dispatch_gemm_pair(const void* A, const void* B, void* C, int M, int 
     else p.group_m = (a_bytes <= 64e6) ? num_m : 4;
     p.a_policy = p.b_policy = kL2EvictNormal;
     const int clusters = std::min(num_m * num_n, g_pair_clusters);
-    if (!a_mn && !b_mn) return launch_gemm_pair<false, false>(tmA, tmB, tmC, tmAux, p, clusters, stream);
-    if (!a_mn && b_mn)  return launch_gemm_pair<false, true>(tmA, tmB, tmC, tmAux, p, clusters, stream);
-    if (a_mn && !b_mn)  return launch_gemm_pair<true, false>(tmA, tmB, tmC, tmAux, p, clusters, stream);
-    return launch_gemm_pair<true, true>(tmA, tmB, tmC, tmAux, p, clusters, stream);
+    if (!a_mn && !b_mn) return launch_gemm_pair<false, false, LOWREG>(tmA, tmB, tmC, tmAux, p, clusters, stream);
+    if (!a_mn && b_mn)  return launch_gemm_pair<false, true, LOWREG>(tmA, tmB, tmC, tmAux, p, clusters, stream);
+    if (a_mn && !b_mn)  return launch_gemm_pair<true, false, LOWREG>(tmA, tmB, tmC, tmAux, p, clusters, stream);
+    return launch_gemm_pair<true, true, LOWREG>(tmA, tmB, tmC, tmAux, p, clusters, stream);
 }
 
 template <int BN, bool A_MN, bool B_MN>
@@ -164,7 +170,7 @@ static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 
 extern "C" {
 
 void dlbb_gemm_set_tile_n(int bn) { dlbb::g_force_bn = (bn == 128 || bn == 256) ? bn : 0; }
-void dlbb_gemm_set_pair_mode(int mode) { dlbb::g_pair_mode = (mode == 0 || mode == 1) ? mode : -1; }
+void dlbb_gemm_set_pair_mode(int mode) { dlbb::g_pair_mode = (mode >= 0 && mode <= 2) ? mode : -1; }
 
 int dlbb_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K, int64_t lda,
                    int64_t ldb, int64_t ldc, int a_mn_major, int b_mn_major, int epilogue,
@@ -185,11 +191,15 @@ int dlbb_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K, i
     int bn = g_force_bn;
     if (g_pair_mode < 0) {
         const char* e = getenv("DLBB_GEMM_PAIR");
-        g_pair_mode = (e && atoi(e) == 0) ? 0 : 1;
+        g_pair_mode = e ? std::max(0, std::min(2, atoi(e))) : 2;
     }
-    if (g_pair_mode == 1 && bn == 0 && M > kBM && N > 128)
-        return dispatch_gemm_pair(A, B, C, M, N, K, lda, ldb, ldc, a_mn_major, b_mn_major, epilogue, aux,
-                                  ld_aux, s);
+    if (g_pair_mode >= 1 && bn == 0 && M > kBM && N > 128) {
+        if (g_pair_mode == 2)
+            return dispatch_gemm_pair<true>(A, B, C, M, N, K, lda, ldb, ldc, a_mn_major, b_mn_major, epilogue, aux,
+                                            ld_aux, s);
+        return dispatch_gemm_pair<false>(A, B, C, M, N, K, lda, ldb, ldc, a_mn_major, b_mn_major, epilogue, aux,
+                                         ld_aux, s);
+    }
     if (bn == 0) {
         // Measured on B200 (profiles/gemm_shapes.md): the 128-wide tile is shared-memory-bandwidth
         // bound (A and B are re-read at 128 B/clk/SM) and loses ~30% to the 256-wide tile on every

@@ -54,8 +54,9 @@ int dlbb_gemm_bf16_simt(const void* A, const void* B, void* C, int M, int N, int
                         void* aux, int64_t ld_aux, void* stream);
 /* Tuning knob: 0 = auto, 128 or 256 = force the N tile. */
 void dlbb_gemm_set_tile_n(int bn);
-/* Tuning knob: 1 = 256 x 256 tiles on CTA pairs (tcgen05.mma.cta_group::2, cluster of two), 0 = one CTA per
- * 128 x 256 tile, -1 = take DLBB_GEMM_PAIR from the environment (the default). */
+/* Tuning knob: 2 = 256 x 256 tiles on CTA pairs (tcgen05.mma.cta_group::2, cluster of two) built with at most 168
+ * registers per thread so that a second kernel can share the SMs (the default), 1 = the same without the register cap,
+ * 0 = one CTA per 128 x 256 tile, -1 = take DLBB_GEMM_PAIR from the environment (default 2). */
 void dlbb_gemm_set_pair_mode(int mode);
 
 /* ------------------------------------------------------------------------------------------

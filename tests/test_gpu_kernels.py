@@ -45,13 +45,13 @@ def test_gemm_cta_pair_matches_one_cta_bitwise(native_lib, ta, tb, shape):
     ref = (a.t() if ta else a).float() @ (b.t() if tb else b).float()
     outs = []
     try:
-        for mode in (1, 0):
+        for mode in (2, 1, 0):     # capped-register pair build (default), uncapped pair build, one CTA
             native_lib.dlbb_gemm_set_pair_mode(mode)
             outs.append(ops.matmul(a, b, transpose_a=ta, transpose_b=tb))
     finally:
         native_lib.dlbb_gemm_set_pair_mode(-1)
     assert relerr(outs[0], ref) < 6e-3
-    assert torch.equal(outs[0], outs[1])
+    assert torch.equal(outs[0], outs[2]) and torch.equal(outs[1], outs[2])
 
 
 @pytest.mark.parametrize("epi", ["gelu", "add", "mul_dgelu"])

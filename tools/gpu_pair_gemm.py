@@ -20,7 +20,7 @@ def relerr(a, b):
 
 
 def case(M, N, K, ta, tb, epi, pad=0):
-    for mode in (1,):
+    for mode in (1, 2):
         case_mode(M, N, K, ta, tb, epi, pad, mode)
 
 
@@ -113,7 +113,7 @@ if ok_all:
         aux = torch.randn(M, N, device=dev).bfloat16() if epi else None
         A = a.t() if ta else a; B = b.t() if tb else b
         variants = {}
-        for mode, key in ((0, "one_cta"), (1, "pair")):
+        for mode, key in ((0, "one_cta"), (1, "pair"), (2, "pair_r168")):
             def plain(mode=mode):
                 lib.dlbb_gemm_set_pair_mode(mode)
                 ops.matmul(a, b, transpose_a=ta, transpose_b=tb, out=out)
@@ -136,7 +136,7 @@ if ok_all:
         row = dict(name=name, M=M, N=N, K=K, ta=ta, tb=tb, epi=epi)
         for k, v in samples.items():
             row[k + "_ms"] = round(statistics.median(v), 5)
-        for k in ("one_cta", "pair", "cublas"):
+        for k in ("one_cta", "pair", "pair_r168", "cublas"):
             row[k + "_tflops"] = round(2.0 * M * N * K / row[k + "_ms"] / 1e9, 1)
         res["perf"].append(row); print("PERF", json.dumps(row), flush=True)
     lib.dlbb_gemm_set_pair_mode(-1)

@@ -42,9 +42,10 @@ def check(name, got, ref, tol=0.0):
 
 
 TOL = {torch.bfloat16: 2e-2, torch.float16: 4e-3, torch.float32: 1e-5, torch.float64: 1e-12}
+ROUNDS = 0 if os.environ.get("ZC_SKIP_NUMERICS") == "1" else 2   # perf-only runs on the expensive 8-GPU box
 try:
     comm.set_zero_copy_min_bytes(1)          # every size goes zero-copy
-    for rnd in range(2):                     # second round: new tensors -> other allocations / cached mappings
+    for rnd in range(ROUNDS):                     # second round: new tensors -> other allocations / cached mappings
         for dtype in (torch.bfloat16, torch.float32, torch.float64):
             tol = TOL[dtype]
             for n in (1000, (1 << 18) + 8, (5 << 20) + 3):
