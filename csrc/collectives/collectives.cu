@@ -686,6 +686,149 @@ allreduce_pipelined_kernel(CommDev c, const T* __restrict__ src, T* __restrict__
 }
 
 // ------------------------------------------------------------------------------------------
+// K5/K7 for large messages on more than two ranks: pipelined chains.
+//
+// A single root that pulls from (or is pulled by) world-1 peers moves the message world-1 times over its own
+// link, and the multicast forms are limited by what one GPU can issue as multimem traffic (measured at 8 GPUs,
+// 512 MiB: broadcast 388 GB/s with multimem.st, reduce 272 GB/s with multimem.ld_reduce, NCCL ~600 for both).  In a
+// chain every link carries the message exactly once and all links work at the same time:
+//
+//   broadcast:  root -> root+1 -> ... -> root-1      each rank pulls chunk k out of its predecessor's staging
+//                                                     into its tensor and into its own staging for the successor
+//   reduce:     root+1 -> root+2 -> ... -> root       each rank adds its own chunk k to the predecessor's partial
+//                                                     sum (fp32 add, partials travel in the tensor's dtype - the
+//                                                     same rounding a ring reduction has) and the root writes dst
+//
+// CTA b owns byte range b on every rank and walks it in 64 KiB chunks; "chunk k is in my staging" travels as a
+// one-directional flag on the successor's signal pad (bank 4, epoch = base + k + 1), so a rank works on chunk k
+// while its predecessor already produces chunk k+1.  A closing row barrier bounds the skew between ranks (nobody
+// re-uses the staging region while a neighbour still reads it).  Everything goes through symmetric staging, so
+// any tensor (any allocator, any alignment) can take this path.
+constexpr int kChainChunkVecs = 4096;   // 64 KiB
+constexpr int kChainBank = 4;
+
+__device__ __forceinline__ uint4 ld_any_v4(const char* p, bool vec) {   // 16 bytes from a possibly unaligned local pointer
+    if (vec) return ld_stream_v4(p);
+    uint4 v;
+    char* vb = reinterpret_cast<char*>(&v);
+#pragma unroll
+    for (int b = 0; b < 16; ++b) vb[b] = p[b];
+    return v;
+}
+__device__ __forceinline__ void st_any_v4(char* p, const uint4& v, bool vec) {
+    if (vec) { st_v4(p, v); return; }
+    const char* vb = reinterpret_cast<const char*>(&v);
+#pragma unroll
+    for (int b = 0; b < 16; ++b) p[b] = vb[b];
+}
+
+__global__ void __launch_bounds__(kCollThreads)
+chain_broadcast_kernel(CommDev c, const char* __restrict__ src, char* __restrict__ dst, int64_t bytes, int root,
+                       int64_t stage_off, uint32_t flag_base, int nchunks, uint32_t end_epoch) {
+    const int pos = (c.rank - root + c.world) % c.world;
+    const bool first = pos == 0, last = pos == c.world - 1;
+    const int pred = (c.rank + c.world - 1) % c.world, succ = (c.rank + 1) % c.world;
+    const int row = blockIdx.x;
+    const int64_t nvec = bytes >> 4;
+    const int64_t per = (nvec + gridDim.x - 1) / gridDim.x;
+    const int64_t v_lo = min((int64_t)blockIdx.x * per, nvec), v_hi = min(v_lo + per, nvec);
+    const int64_t tail_lo = nvec << 4;   // < 16 trailing bytes ride with chunk 0 of CTA 0
+    const bool src_vec = (reinterpret_cast<uintptr_t>(src) & 15) == 0, dst_vec = (reinterpret_cast<uintptr_t>(dst) & 15) == 0;
+    char* mine = c.stage[c.rank] + stage_off;
+    const char* theirs = c.stage[pred] + stage_off;
+    for (int k = 0; k < nchunks; ++k) {
+        const int64_t c_lo = min(v_lo + (int64_t)k * kChainChunkVecs, v_hi), c_hi = min(c_lo + kChainChunkVecs, v_hi);
+        if (!first) {
+            if (threadIdx.x == 0) wait_flag(pad_slot(c, c.rank, kChainBank, row, pred), flag_base + k + 1, pred);
+            __syncthreads();
+        }
+        for (int64_t i0 = c_lo + threadIdx.x; i0 < c_hi; i0 += (int64_t)blockDim.x * kU) {
+            uint4 v[kU];
+#pragma unroll
+            for (int u = 0; u < kU; ++u) {
+                const int64_t i = i0 + u * blockDim.x;
+                if (i < c_hi) v[u] = first ? ld_any_v4(src + (i << 4), src_vec) : ld_peer_v4(theirs + (i << 4));
+            }
+#pragma unroll
+            for (int u = 0; u < kU; ++u) {
+                const int64_t i = i0 + u * blockDim.x;
+                if (i >= c_hi) continue;
+                if (!last) st_v4(mine + (i << 4), v[u]);
+                if (!first) st_any_v4(dst + (i << 4), v[u], dst_vec);
+            }
+        }
+        if (row == 0 && k == 0) {
+            for (int64_t b = tail_lo + threadIdx.x; b < bytes; b += blockDim.x) {
+                const char x = first ? src[b] : ld_peer_scalar(theirs + b);
+                if (!last) mine[b] = x;
+                if (!first) dst[b] = x;
+            }
+        }
+        if (!last) {
+            __syncthreads();
+            if (threadIdx.x == 0) st_release_sys(pad_slot(c, succ, kChainBank, row, c.rank), flag_base + k + 1);
+        }
+    }
+    row_barrier(c, 0, row, end_epoch);
+}
+
+template <typename T, int OP>
+__global__ void __launch_bounds__(kCollThreads)
+chain_reduce_kernel(CommDev c, const T* __restrict__ src, T* __restrict__ dst, int64_t n, int root, int64_t stage_off,
+                    uint32_t flag_base, int nchunks, uint32_t end_epoch) {
+    constexpr int VE = 16 / sizeof(T);
+    using A = typename Acc<T>::type;
+    const int pos = (c.rank - root - 1 + 2 * c.world) % c.world;   // the chain starts at root+1 and ends at the root
+    const bool first = pos == 0, last = pos == c.world - 1;
+    const int pred = (c.rank + c.world - 1) % c.world, succ = (c.rank + 1) % c.world;
+    const int row = blockIdx.x;
+    const int64_t nvec = n / VE;   // n is a multiple of VE (the host reduces a ragged tail separately)
+    const int64_t per = (nvec + gridDim.x - 1) / gridDim.x;
+    const int64_t v_lo = min((int64_t)blockIdx.x * per, nvec), v_hi = min(v_lo + per, nvec);
+    const bool src_vec = (reinterpret_cast<uintptr_t>(src) & 15) == 0, dst_vec = (reinterpret_cast<uintptr_t>(dst) & 15) == 0;
+    char* mine = c.stage[c.rank] + stage_off;
+    const char* theirs = c.stage[pred] + stage_off;
+    const char* srcb = reinterpret_cast<const char*>(src);
+    for (int k = 0; k < nchunks; ++k) {
+        const int64_t c_lo = min(v_lo + (int64_t)k * kChainChunkVecs, v_hi), c_hi = min(c_lo + kChainChunkVecs, v_hi);
+        if (!first) {
+            if (threadIdx.x == 0) wait_flag(pad_slot(c, c.rank, kChainBank, row, pred), flag_base + k + 1, pred);
+            __syncthreads();
+        }
+        for (int64_t i0 = c_lo + threadIdx.x; i0 < c_hi; i0 += (int64_t)blockDim.x * kU) {
+            uint4 own[kU], part[kU];
+#pragma unroll
+            for (int u = 0; u < kU; ++u) {
+                const int64_t i = i0 + u * blockDim.x;
+                if (i < c_hi) {
+                    if (!first) part[u] = ld_peer_v4(theirs + (i << 4));
+                    own[u] = ld_any_v4(srcb + (i << 4), src_vec);
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < kU; ++u) {
+                const int64_t i = i0 + u * blockDim.x;
+                if (i >= c_hi) continue;
+                uint4 o = own[u];
+                if (!first) {
+                    T* ot = reinterpret_cast<T*>(&o);
+                    const T* pt = reinterpret_cast<const T*>(&part[u]);
+#pragma unroll
+                    for (int e = 0; e < VE; ++e) ot[e] = from_acc<T>(red_op<OP, A>(to_acc<T>(pt[e]), to_acc<T>(ot[e])));
+                }
+                if (last) st_any_v4(reinterpret_cast<char*>(dst) + (i << 4), o, dst_vec);
+                else st_v4(mine + (i << 4), o);
+            }
+        }
+        if (!last) {
+            __syncthreads();
+            if (threadIdx.x == 0) st_release_sys(pad_slot(c, succ, kChainBank, row, c.rank), flag_base + k + 1);
+        }
+    }
+    row_barrier(c, 0, row, end_epoch);
+}
+
+// ------------------------------------------------------------------------------------------
 // K11: point-to-point.  Only the two ranks of a message take part, so it has its own staging region
 // (one slot per destination inside the sender's region), its own pad bank and per-pair epochs:
 //   sender:   wait until the receiver has consumed the previous message of this pair (ack flag),
@@ -970,6 +1113,61 @@ static int launch_allreduce_direct(dlbb_comm* c, int dtype, int op, const PeerVi
     return -2;
 }
 
+// ---- chain launches (large broadcast / reduce on more than two ranks)
+// Opt-in (DLBB_CHAIN_MIN_BYTES=<bytes>): validated on 4 GPUs with the chains forced at every size (97 checks,
+// profiles/raw/zero_copy_4gpu_chain_forced.json), but there they only match the multicast forms (broadcast 442 vs
+// 532 GB/s, reduce 428 vs 430 at 512 MiB; NCCL 628): one CTA handles wait -> load -> store -> signal of a chunk
+// strictly in sequence (~19 us per 64 KiB).  Overlapping the next chunk's loads with the signalling is the open item.
+static int64_t chain_min_bytes() {
+    static const int64_t v = getenv("DLBB_CHAIN_MIN_BYTES") ? atoll(getenv("DLBB_CHAIN_MIN_BYTES")) : 0;
+    return v;   // <= 0: chains off (the default)
+}
+struct ChainGeom { int ctas; int nchunks; uint32_t flag_base; int64_t stage_off; uint32_t end_epoch; };
+static ChainGeom chain_geom(dlbb_comm* c, int64_t nvec) {
+    ChainGeom g;
+    g.ctas = c->ctas > 0 ? std::min(c->ctas, kMaxCtas) : 128;
+    const int64_t per = (nvec + g.ctas - 1) / g.ctas;
+    g.nchunks = static_cast<int>(std::max<int64_t>(1, (per + kChainChunkVecs - 1) / kChainChunkVecs));
+    g.flag_base = c->epoch[kChainBank];
+    c->epoch[kChainBank] += g.nchunks;
+    g.stage_off = next_stage_off(c);
+    g.end_epoch = ++c->epoch[0];
+    return g;
+}
+
+template <typename T, int OP>
+static int launch_chain_reduce_T(dlbb_comm* c, const void* src, void* dst, int64_t n, int root, cudaStream_t s) {
+    const ChainGeom g = chain_geom(c, n / (16 / (int64_t)sizeof(T)));
+    chain_reduce_kernel<T, OP><<<g.ctas, kCollThreads, 0, s>>>(c->dev, static_cast<const T*>(src), static_cast<T*>(dst), n,
+                                                              root, g.stage_off, g.flag_base, g.nchunks, g.end_epoch);
+    DLBB_CHECK_LAUNCH("chain_reduce_kernel");
+    return 0;
+}
+template <typename T>
+static int launch_chain_reduce_op(dlbb_comm* c, int op, const void* src, void* dst, int64_t n, int root, cudaStream_t s) {
+    switch (op) {
+        case DLBB_SUM: return launch_chain_reduce_T<T, DLBB_SUM>(c, src, dst, n, root, s);
+        case DLBB_MAX: return launch_chain_reduce_T<T, DLBB_MAX>(c, src, dst, n, root, s);
+        case DLBB_MIN: return launch_chain_reduce_T<T, DLBB_MIN>(c, src, dst, n, root, s);
+        case DLBB_PROD: return launch_chain_reduce_T<T, DLBB_PROD>(c, src, dst, n, root, s);
+    }
+    set_error("unknown reduce op %d", op);
+    return -2;
+}
+static int launch_chain_reduce(dlbb_comm* c, int dtype, int op, const void* src, void* dst, int64_t n, int root,
+                               cudaStream_t s) {
+    switch (dtype) {
+        case DLBB_F16: return launch_chain_reduce_op<__half>(c, op, src, dst, n, root, s);
+        case DLBB_BF16: return launch_chain_reduce_op<__nv_bfloat16>(c, op, src, dst, n, root, s);
+        case DLBB_F32: return launch_chain_reduce_op<float>(c, op, src, dst, n, root, s);
+        case DLBB_F64: return launch_chain_reduce_op<double>(c, op, src, dst, n, root, s);
+        case DLBB_I32: return launch_chain_reduce_op<int32_t>(c, op, src, dst, n, root, s);
+        case DLBB_I64: return launch_chain_reduce_op<int64_t>(c, op, src, dst, n, root, s);
+    }
+    set_error("reduction on unsupported dtype %d", dtype);
+    return -2;
+}
+
 static int allreduce_impl(dlbb_comm* c, const void* in, void* out, const void* extra, int64_t count, int dtype, int op,
                           int algo, const dlbb_view_t* in_view, cudaStream_t s) {
     const size_t es = dtype_size(dtype);
@@ -1068,6 +1266,28 @@ int dlbb_reduce(dlbb_comm_t* c, const void* in, void* out, int64_t count, int dt
     const int64_t VE = 16 / (int64_t)es;
     const bool nvls_ok = dlbb_comm_has_multicast(c) && op == DLBB_SUM &&
                          (dtype == DLBB_F16 || dtype == DLBB_BF16 || dtype == DLBB_F32);
+    if (c->world > 2 && chain_min_bytes() > 0 && count * (int64_t)es >= chain_min_bytes()) {
+        // Large message, several senders: pipelined chain ending at the root, every link carries the message once.
+        const int64_t cap2 = static_cast<int64_t>(c->stage_bytes / es) / VE * VE;
+        int64_t done = 0;
+        while (count - done >= VE) {
+            const int64_t n = std::min(count - done, cap2) / VE * VE;
+            const int rc = launch_chain_reduce(c, dtype, op, static_cast<const char*>(in) + done * es,
+                                               static_cast<char*>(out) + done * es, n, root, static_cast<cudaStream_t>(stream));
+            if (rc) return rc;
+            done += n;
+        }
+        if (done < count) {   // fewer than 16 bytes left: single-barrier form
+            const int64_t n = count - done;
+            PieceList pack{};
+            pack.count = 1;
+            pack.p[0] = Piece{0, done, 0, n};
+            const int rc = launch_reduce(c, dtype, op, in, static_cast<char*>(out) + done * es, nullptr, pack, ViewDev{}, 0,
+                                         c->rank == root ? n : 0, n * es, static_cast<cudaStream_t>(stream));
+            if (rc) return rc;
+        }
+        return 0;
+    }
     if (c->world > 2 && (nvls_ok || count * (int64_t)es > (512 << 10))) {
         // More than one sender: a root that pulls everything is limited by its own link ((world-1) x the message;
         // measured at 8 GPUs, 128 MiB: 109 GB/s).  Use the all-reduce data flow instead - every rank reduces
@@ -1193,6 +1413,18 @@ int dlbb_broadcast(dlbb_comm_t* c, void* buf, int64_t count, int dtype, int root
     DLBB_REQUIRE(es != 0, "broadcast: unsupported dtype %d", dtype);
     DLBB_REQUIRE(root >= 0 && root < c->world, "broadcast: bad root %d", root);
     const int64_t total = count * es, cap = static_cast<int64_t>(c->stage_bytes) / 64 * 64;
+    if (c->world > 2 && chain_min_bytes() > 0 && total >= chain_min_bytes()) {
+        // Large message, several receivers: pipelined chain, every link carries the message once.
+        for (int64_t done = 0; done < total; done += cap) {
+            const int64_t n = std::min(cap, total - done);
+            const ChainGeom g = chain_geom(c, n >> 4);
+            chain_broadcast_kernel<<<g.ctas, kCollThreads, 0, static_cast<cudaStream_t>(stream)>>>(
+                c->dev, static_cast<const char*>(buf) + done, static_cast<char*>(buf) + done, n, root, g.stage_off,
+                g.flag_base, g.nchunks, g.end_epoch);
+            DLBB_CHECK_LAUNCH("chain_broadcast_kernel");
+        }
+        return 0;
+    }
     if (c->world > 2 && dlbb_comm_has_multicast(c)) {
         // More than one receiver: one multicast store through the switch instead of world-1 pulls from the root
         // (measured at 8 GPUs, 128 MiB: 109 GB/s for the pull forms - the root's link carries the message 7 times).

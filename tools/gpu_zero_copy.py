@@ -42,7 +42,8 @@ def check(name, got, ref, tol=0.0):
 
 
 TOL = {torch.bfloat16: 2e-2, torch.float16: 4e-3, torch.float32: 1e-5, torch.float64: 1e-12}
-ROUNDS = 0 if os.environ.get("ZC_SKIP_NUMERICS") == "1" else 2   # perf-only runs on the expensive 8-GPU box
+ROUNDS = 0 if os.environ.get("ZC_SKIP_NUMERICS") == "1" else int(os.environ.get("ZC_ROUNDS", "2"))   # 0: perf only
+PERF_OPS = os.environ.get("ZC_PERF_OPS", "allreduce,allgather,broadcast,reduce,reduce_scatter,alltoall").split(",")
 try:
     comm.set_zero_copy_min_bytes(1)          # every size goes zero-copy
     for rnd in range(ROUNDS):                     # second round: new tensors -> other allocations / cached mappings
@@ -84,6 +85,16 @@ try:
                 o = xs[rank].clone(); comm.reduce(o, root=root)
                 if rank == root: check(f"reduce_{dn}", o, sum(v.double() for v in xs).to(dtype), tol)
                 del xs, bigs, out, big
+    if world > 2:
+        # large broadcast / reduce on unaligned views (the chain kernels take any alignment)
+        n = 9 * (1 << 20) + 5
+        xs = [gen(r, n, torch.bfloat16, seed=31) for r in range(world)]
+        big = torch.zeros(n + 64, dtype=torch.bfloat16, device=dev); v = big[1:1 + n]; v.copy_(xs[rank])
+        comm.broadcast(v, root=1); check("broadcast_unaligned_18MiB", v, xs[1])
+        check("broadcast_unaligned_guard", torch.stack([big[0], big[1 + n]]).float(), torch.zeros(2, device=dev))
+        v.copy_(xs[rank]); comm.reduce(v, root=world - 1)
+        if rank == world - 1: check("reduce_unaligned_18MiB", v, sum(t.double() for t in xs).to(torch.bfloat16), 3e-2)
+        del xs, big
     # results identical on every rank
     x = gen(rank, 100003 * 8, torch.bfloat16, seed=9); comm.all_reduce(x)
     g = [torch.empty_like(x) for _ in range(world)]; dist.all_gather(g, x)
@@ -119,7 +130,7 @@ if flag.item() == 1 and os.environ.get("DLBB_SKIP_PERF") != "1":
     try:
         ZC, STAGED = 1, 1 << 40
         f = 2.0 * (world - 1) / world
-        for nbytes in (1 << 22, 1 << 25, 1 << 27, 1 << 30):
+        for nbytes in ((1 << 22, 1 << 25, 1 << 27, 1 << 30) if "allreduce" in PERF_OPS else ()):
             n = nbytes // 2
             x = torch.ones(n, dtype=torch.bfloat16, device=dev)
             iters = 20 if nbytes <= (1 << 25) else (8 if nbytes <= (1 << 27) else 4)
@@ -151,6 +162,7 @@ if flag.item() == 1 and os.environ.get("DLBB_SKIP_PERF") != "1":
                              wide.numel() * 2 * (world - 1) / world),
             }
             for op, (ours, nccl, wire) in ops_.items():
+                if op not in PERF_OPS: continue
                 row = {"op": op, "bytes": nbytes}
                 for name, zc in (("zero_copy", ZC), ("staged", STAGED)):
                     comm.set_zero_copy_min_bytes(zc)
