@@ -7,34 +7,27 @@
 // once (cached) and the collective receives one pointer per rank to the same logical buffer.
 //
 // The exchange happens on the host at enqueue time, once per large collective, through a tiny
-// shared-memory mailbox (one memfd per rank, mapped by everyone at communicator creation): rank r
-// publishes {sequence, handle, offset} in its own slot and spins until every peer's slot carries the
-// same sequence number - about a microsecond when the peers are already there.  All ranks see the
+// shared-memory mailbox (mailbox.h: one memfd per rank, mapped by everyone at communicator creation;
+// rank r publishes {sequence, handle, offset} in its own slot and spins until every peer's slot carries
+// the same sequence number - about a microsecond when the peers are already there).  All ranks see the
 // same set of "ok" flags, so they take the same decision (zero-copy or staged) without another round.
 //
 // No counterpart in the reference (its tensors live in host memory and go through MPI / Gloo / oneCCL);
 // the closest analogue is NCCL's user-buffer registration.
 #include <cuda.h>
 #include <cuda_runtime.h>
-#include <sched.h>
 #include <string.h>
-#include <sys/mman.h>
-#include <time.h>
-#include <unistd.h>
-
-#include <atomic>
 
 #include "comm_internal.h"
+#include "mailbox.h"
 
 namespace dlbb {
 void set_error(const char* fmt, ...);  // common.cu
 
 namespace {
 
-constexpr int kMailSlots = 4;   // a rank can be at most one exchange ahead of its slowest peer; 4 is slack
-
-struct MailSlot {
-    std::atomic<uint64_t> seq;
+// What a rank tells the others about its buffer (one HostMailbox record).
+struct BufferRecord {
     uint32_t ok;
     uint32_t reserved;
     uint64_t offset;        // of the tensor inside its allocation
@@ -42,21 +35,13 @@ struct MailSlot {
     uint64_t alloc_size;
     unsigned char handle[sizeof(cudaIpcMemHandle_t)];
 };
-struct MailRegion {
-    MailSlot slot[kMailSlots];
-};
+static_assert(sizeof(BufferRecord) <= HostMailbox::kPayload, "record must fit a mailbox slot");
 
 struct PeerMapping {
     unsigned char handle[sizeof(cudaIpcMemHandle_t)];
     uint64_t remote_base, size;
     char* local;            // where the peer's allocation is mapped in this process
 };
-
-double now_s() {
-    timespec ts;
-    clock_gettime(CLOCK_MONOTONIC, &ts);
-    return ts.tv_sec + 1e-9 * ts.tv_nsec;
-}
 
 typedef CUresult (*GetAddressRangeFn)(CUdeviceptr*, size_t*, CUdeviceptr);
 GetAddressRangeFn get_address_range_fn() {
@@ -77,8 +62,7 @@ GetAddressRangeFn get_address_range_fn() {
 
 struct PeerRegistry {
     int rank = 0, world = 1;
-    MailRegion* regions[DLBB_MAX_RANKS] = {};
-    uint64_t seq = 0;
+    HostMailbox mailbox;
     std::vector<PeerMapping> cache[DLBB_MAX_RANKS];
     bool usable = false;
 };
@@ -89,54 +73,32 @@ PeerRegistry* peer_registry_create(dlbb_comm* c) {
     PeerRegistry* r = new PeerRegistry();
     r->rank = c->rank; r->world = c->world;
     if (c->world == 1) return r;
-    int fd = memfd_create("dlbb-mailbox", 0);
-    bool ok = fd >= 0 && ftruncate(fd, sizeof(MailRegion)) == 0;
-    std::vector<int> fds;
-    if (!c->bs->allgather_fds(ok ? fd : STDIN_FILENO, fds)) ok = false;   // every rank must take part
-    if (ok) {
-        for (int p = 0; p < c->world; ++p) {
-            void* m = mmap(nullptr, sizeof(MailRegion), PROT_READ | PROT_WRITE, MAP_SHARED, fds[p], 0);
-            if (m == MAP_FAILED) { ok = false; break; }
-            r->regions[p] = static_cast<MailRegion*>(m);
-        }
-    }
-    for (int f : fds)
-        if (f >= 0) close(f);
-    if (fd >= 0) close(fd);
-    // agreement + IPC self-test
-    char mine = ok ? 1 : 0;
+    if (!r->mailbox.create(*c->bs)) return r;
+    void* probe = nullptr;
+    const bool good = cudaMalloc(&probe, 1 << 20) == cudaSuccess;
+    PeerView pv;
+    bool all_ok = false;
+    r->usable = true;   // resolve() below needs it
+    if (peer_registry_resolve(c, r, good ? probe : nullptr, 1 << 20, &pv, &all_ok) != 0) all_ok = false;
+    char mine = all_ok ? 1 : 0;   // an import can fail on one rank only: agree once more
     std::vector<char> all(c->world);
     c->bs->allgather(&mine, all.data(), 1);
-    for (char v : all) ok = ok && v;
-    if (ok) {
-        void* probe = nullptr;
-        bool good = cudaMalloc(&probe, 1 << 20) == cudaSuccess;
-        PeerView pv;
-        bool all_ok = false;
-        r->usable = true;   // resolve() below needs it
-        if (peer_registry_resolve(c, r, good ? probe : nullptr, 1 << 20, &pv, &all_ok) != 0) all_ok = false;
-        mine = all_ok ? 1 : 0;   // an import can fail on one rank only: agree once more
-        c->bs->allgather(&mine, all.data(), 1);
-        for (char v : all) all_ok = all_ok && v;
-        r->usable = all_ok;
-        // drop the probe mappings again
-        for (int p = 0; p < c->world; ++p) {
-            for (auto& m : r->cache[p]) cudaIpcCloseMemHandle(m.local);
-            r->cache[p].clear();
-        }
-        c->bs->barrier();
-        if (probe) cudaFree(probe);
-        cudaGetLastError();
+    for (char v : all) all_ok = all_ok && v;
+    r->usable = all_ok;
+    for (int p = 0; p < c->world; ++p) {   // drop the probe mappings again
+        for (auto& m : r->cache[p]) cudaIpcCloseMemHandle(m.local);
+        r->cache[p].clear();
     }
+    c->bs->barrier();
+    if (probe) cudaFree(probe);
+    cudaGetLastError();
     return r;
 }
 
 void peer_registry_destroy(PeerRegistry* r) {
     if (!r) return;
-    for (int p = 0; p < r->world; ++p) {
+    for (int p = 0; p < r->world; ++p)
         for (auto& m : r->cache[p]) cudaIpcCloseMemHandle(m.local);
-        if (r->regions[p]) munmap(r->regions[p], sizeof(MailRegion));
-    }
     cudaGetLastError();
     delete r;
 }
@@ -146,11 +108,12 @@ bool peer_registry_usable(const PeerRegistry* r) { return r && r->usable; }
 // Collective and host-blocking: every rank calls it with its own buffer, in the same order.
 // *all_ok is the same on every rank; when false, pv is not filled and the caller falls back to staging.
 int peer_registry_resolve(dlbb_comm* c, PeerRegistry* r, const void* ptr, size_t bytes, PeerView* pv, bool* all_ok) {
+    (void)c;
     *all_ok = false;
     if (!r || !r->usable || r->world == 1) return 0;
-    const uint64_t seq = ++r->seq;
-    MailSlot& mine = r->regions[r->rank]->slot[seq % kMailSlots];
     // ---- export my allocation
+    BufferRecord mine;
+    memset(&mine, 0, sizeof(mine));
     cudaIpcMemHandle_t h;
     memset(&h, 0, sizeof(h));
     CUdeviceptr base = 0;
@@ -167,31 +130,22 @@ int peer_registry_resolve(dlbb_comm* c, PeerRegistry* r, const void* ptr, size_t
     mine.alloc_base = base;
     mine.alloc_size = asize;
     memcpy(mine.handle, &h, sizeof(h));
-    mine.seq.store(seq, std::memory_order_release);
-    // ---- wait for everyone's slot of this exchange
-    const double t0 = now_s();
-    bool everyone = ok;
-    for (int p = 0; p < r->world; ++p) {
-        if (p == r->rank) continue;
-        MailSlot& s = r->regions[p]->slot[seq % kMailSlots];
-        unsigned spins = 0;
-        while (s.seq.load(std::memory_order_acquire) != seq) {
-            if ((++spins & 0xff) == 0) {
-                sched_yield();
-                if (now_s() - t0 > 120.0) {
-                    set_error("zero-copy exchange %llu: rank %d did not arrive within 120 s (ranks must issue large "
-                              "collectives in the same order)", (unsigned long long)seq, p);
-                    return -1;
-                }
-            }
-        }
-        everyone = everyone && s.ok;
+    // ---- everybody's record of this exchange
+    const void* recs[HostMailbox::kMaxRanks];
+    int missing = -1;
+    if (!r->mailbox.exchange(&mine, sizeof(mine), recs, 120.0, &missing)) {
+        set_error("zero-copy exchange %llu: rank %d did not arrive within 120 s (ranks must issue large collectives in "
+                  "the same order)", (unsigned long long)r->mailbox.sequence(), missing);
+        return -1;
     }
+    bool everyone = true;
+    for (int p = 0; p < r->world; ++p) everyone = everyone && static_cast<const BufferRecord*>(recs[p])->ok;
     if (!everyone) return 0;
     // ---- map the peers' allocations (cached by handle)
     for (int p = 0; p < r->world; ++p) {
         if (p == r->rank) { pv->ptr[p] = static_cast<char*>(const_cast<void*>(ptr)); continue; }
-        const MailSlot& s = r->regions[p]->slot[seq % kMailSlots];
+        BufferRecord s;
+        memcpy(&s, recs[p], sizeof(s));
         char* local = nullptr;
         auto& cache = r->cache[p];
         for (size_t i = 0; i < cache.size(); ++i) {
