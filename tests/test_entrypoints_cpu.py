@@ -40,6 +40,25 @@ def test_launcher_mpirun_flags_and_failure_propagation(tmp_path):
     assert r.returncode == 7
 
 
+def test_launcher_under_address_sanitizer(tmp_path):
+    """SURVEY 5.2 for the launcher: the same binary built with ASan + UBSan spawns, binds, forwards the environment
+    and propagates a failing rank's exit code without a sanitizer report."""
+    exe = tmp_path / "b200run_asan"
+    srcs = sorted((ROOT / "csrc" / "launcher").glob("*.cpp"))
+    b = subprocess.run(["g++", "-O1", "-g", "-std=c++17", "-fsanitize=address,undefined", "-fno-sanitize-recover=all",
+                        "-o", str(exe), *map(str, srcs), "-lpthread", "-ldl"], capture_output=True, text=True)
+    if b.returncode != 0:
+        pytest.skip(f"sanitizer runtime not available: {b.stderr[-300:]}")
+    script = tmp_path / "p.py"
+    script.write_text("import os,sys\nprint('R', os.environ['RANK'])\nsys.exit(5 if os.environ['RANK']=='1' and len(sys.argv)>1 else 0)\n")
+    env = {"ASAN_OPTIONS": "detect_leaks=0:halt_on_error=1"}
+    r = run([exe, "--as", "mpirun", "-np", 2, "--map-by", "slot:PE=1", "-x", "FOO=bar", sys.executable, script], env=env)
+    assert r.returncode == 0 and "ERROR: AddressSanitizer" not in r.stderr and "runtime error" not in r.stderr, r.stderr[-3000:]
+    assert sorted(l for l in r.stdout.splitlines() if l.startswith("R ")) == ["R 0", "R 1"]
+    r = run([exe, "--as", "mpirun", "-np", 2, sys.executable, script, "fail"], env=env)
+    assert r.returncode == 5 and "ERROR: AddressSanitizer" not in r.stderr, r.stderr[-3000:]
+
+
 def test_launcher_deepspeed_flags(tmp_path):
     script = tmp_path / "d.py"
     script.write_text("import os\nprint('D', os.environ['RANK'], os.environ['MASTER_PORT'], os.environ['CUDA_VISIBLE_DEVICES'],"
