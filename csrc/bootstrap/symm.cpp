@@ -359,6 +359,7 @@ int dlbb_comm_create(int rank, int world, int device, const char* job, size_t st
         c->default_algo = a == "oneshot" ? DLBB_ALGO_ONESHOT : a == "twoshot" ? DLBB_ALGO_TWOSHOT
                         : a == "nvls" ? DLBB_ALGO_NVLS : a == "direct" ? DLBB_ALGO_DIRECT : DLBB_ALGO_AUTO;
     }
+    c->debug_poison = getenv("DLBB_DEBUG_POISON") != nullptr && atoi(getenv("DLBB_DEBUG_POISON")) != 0;
     // Zero-copy path for large messages on ordinary allocations (peer_registry.cpp); DLBB_ZEROCOPY_MIN_BYTES=0 disables.
     e = getenv("DLBB_ZEROCOPY_MIN_BYTES");
     c->zero_copy_min = e ? static_cast<size_t>(atoll(e)) : (static_cast<size_t>(16) << 20);

@@ -891,9 +891,19 @@ static int pick_ctas(const dlbb_comm* c, int64_t bytes) {
     return std::min(n, kMaxCtas);
 }
 
-static int64_t next_stage_off(dlbb_comm* c) {
+// Debug aid (DLBB_DEBUG_POISON=1): fill a staging region with 0xFF - NaN in every floating-point
+// format, -1 in the integer ones - on the caller's stream right before the kernel that is going to (re)write it, so a
+// protocol bug that lets a rank read staging data before its producer has written it shows up as NaN / -1 in the result
+// instead of as plausible numbers from an earlier collective.  Safe for the same reason packing into the region is:
+// when this call is issued, every peer has finished reading what the call before last left there.
+static void poison_region(dlbb_comm* c, int64_t off, cudaStream_t s) {
+    if (c->debug_poison) cudaMemsetAsync(c->dev.stage[c->rank] + off, 0xFF, c->stage_bytes, s);
+}
+
+static int64_t next_stage_off(dlbb_comm* c, cudaStream_t s, bool may_poison = true) {
     const int64_t off = (c->parity & 1) ? static_cast<int64_t>(c->stage_bytes) : 0;
     c->parity ^= 1;
+    if (may_poison) poison_region(c, off, s);
     return off;
 }
 
@@ -933,7 +943,7 @@ static int launch_reduce_T(dlbb_comm* c, const void* src, void* dst, const void*
         return 0;
     }
     const int ctas = pick_ctas(c, bytes_hint);
-    const int64_t so = next_stage_off(c);
+    const int64_t so = next_stage_off(c, s);
     const uint32_t ep = ++c->epoch[0];
     reduce_kernel<T, OP><<<ctas, kCollThreads, 0, s>>>(c->dev, static_cast<const T*>(src), static_cast<T*>(dst),
                                                        static_cast<const T*>(extra), pack, view, red_off, red_n, so, 0,
@@ -975,8 +985,9 @@ template <typename T, int OP>
 static int launch_twoshot_T(dlbb_comm* c, bool nvls, const void* src, void* dst, const void* extra, const ViewDev& view,
                             int64_t src_off, int64_t n, cudaStream_t s, int root) {
     const int64_t bytes = n * (int64_t)sizeof(T);
-    const int64_t in_off = next_stage_off(c);
+    const int64_t in_off = next_stage_off(c, s);
     const int64_t out_off = in_off == 0 ? static_cast<int64_t>(c->stage_bytes) : 0;
+    poison_region(c, out_off, s);   // the peers write my out-staging only after they have seen me enter this kernel
     const bool use_nvls = nvls && MmReduce<T>::ok && OP == DLBB_SUM;
     static const int64_t pipe_min = getenv("DLBB_PIPELINE_MIN_BYTES") ? atoll(getenv("DLBB_PIPELINE_MIN_BYTES")) : (8ll << 20);
     if (bytes >= pipe_min && use_nvls && root < 0) {
@@ -1058,7 +1069,7 @@ static int launch_move(dlbb_comm* c, const void* src, void* dst, const PieceList
         return 0;
     }
     const int ctas = pick_ctas(c, bytes_hint);
-    const int64_t so = next_stage_off(c);
+    const int64_t so = next_stage_off(c, s);
     const uint32_t ep = ++c->epoch[0];
     move_kernel<<<ctas, kCollThreads, 0, s>>>(c->dev, static_cast<const char*>(src), static_cast<char*>(dst), pack, pull,
                                               view, elem_size, so, 0, ep, PeerView{}, 0);
@@ -1123,21 +1134,21 @@ static int64_t chain_min_bytes() {
     return v;   // <= 0: chains off (the default)
 }
 struct ChainGeom { int ctas; int nchunks; uint32_t flag_base; int64_t stage_off; uint32_t end_epoch; };
-static ChainGeom chain_geom(dlbb_comm* c, int64_t nvec) {
+static ChainGeom chain_geom(dlbb_comm* c, int64_t nvec, cudaStream_t s) {
     ChainGeom g;
     g.ctas = c->ctas > 0 ? std::min(c->ctas, kMaxCtas) : 128;
     const int64_t per = (nvec + g.ctas - 1) / g.ctas;
     g.nchunks = static_cast<int>(std::max<int64_t>(1, (per + kChainChunkVecs - 1) / kChainChunkVecs));
     g.flag_base = c->epoch[kChainBank];
     c->epoch[kChainBank] += g.nchunks;
-    g.stage_off = next_stage_off(c);
+    g.stage_off = next_stage_off(c, s);
     g.end_epoch = ++c->epoch[0];
     return g;
 }
 
 template <typename T, int OP>
 static int launch_chain_reduce_T(dlbb_comm* c, const void* src, void* dst, int64_t n, int root, cudaStream_t s) {
-    const ChainGeom g = chain_geom(c, n / (16 / (int64_t)sizeof(T)));
+    const ChainGeom g = chain_geom(c, n / (16 / (int64_t)sizeof(T)), s);
     chain_reduce_kernel<T, OP><<<g.ctas, kCollThreads, 0, s>>>(c->dev, static_cast<const T*>(src), static_cast<T*>(dst), n,
                                                               root, g.stage_off, g.flag_base, g.nchunks, g.end_epoch);
     DLBB_CHECK_LAUNCH("chain_reduce_kernel");
@@ -1417,7 +1428,7 @@ int dlbb_broadcast(dlbb_comm_t* c, void* buf, int64_t count, int dtype, int root
         // Large message, several receivers: pipelined chain, every link carries the message once.
         for (int64_t done = 0; done < total; done += cap) {
             const int64_t n = std::min(cap, total - done);
-            const ChainGeom g = chain_geom(c, n >> 4);
+            const ChainGeom g = chain_geom(c, n >> 4, static_cast<cudaStream_t>(stream));
             chain_broadcast_kernel<<<g.ctas, kCollThreads, 0, static_cast<cudaStream_t>(stream)>>>(
                 c->dev, static_cast<const char*>(buf) + done, static_cast<char*>(buf) + done, n, root, g.stage_off,
                 g.flag_base, g.nchunks, g.end_epoch);
@@ -1432,7 +1443,8 @@ int dlbb_broadcast(dlbb_comm_t* c, void* buf, int64_t count, int dtype, int root
             const int64_t n = std::min(cap, total - done);
             const int ctas = c->ctas > 0 ? std::min(c->ctas, kMaxCtas)
                                          : static_cast<int>(std::min<int64_t>(128, std::max<int64_t>(1, n / (64 << 10))));
-            const int64_t so = next_stage_off(c);
+            // (not poisoned: the root may multicast into a receiver's staging before that receiver has entered the kernel)
+            const int64_t so = next_stage_off(c, static_cast<cudaStream_t>(stream), false);
             const int64_t per = ((n >> 4) + ctas - 1) / ctas;
             const int nchunks = static_cast<int>(std::max<int64_t>(1, (per + kBcChunkVecs - 1) / kBcChunkVecs));
             const uint32_t fb = c->epoch[kBcFlagBank];
