@@ -5,7 +5,7 @@ import collections, re, subprocess, sys
 lib = sys.argv[1] if len(sys.argv) > 1 else "distributed_llm_backend_benchmark_b200/lib/libdlbb.so"
 out = subprocess.run(["cuobjdump", "-sass", lib], capture_output=True, text=True).stdout
 demangle = lambda n: subprocess.run(["c++filt", n], capture_output=True, text=True).stdout.strip()
-pat = re.compile(r"\b(UTC[A-Z]*MMA|UTMALDG|UTMASTG|UTMAPF|LDTM|STTM|UTCBAR|UTCATOMSWS|SYNCS|UBLKCP|HMMA|LDG|STG|RED|ATOM|MULTIMEM|LD\.E\.[A-Z0-9.]*STRONG\.SYS|ST\.E\.[A-Z0-9.]*STRONG\.SYS|CCTL)[A-Z0-9_.]*")
+pat = re.compile(r"\b(UTC[A-Z]*MMA|UTMALDG|UTMASTG|UTMAPF|LDTM|STTM|UTCBAR|UTCATOMSWS|SYNCS|UBLKCP|HMMA|LDG|STG|RED|ATOM|MULTIMEM|LDGMC|STGMC|REDGMC|LD\.E\.[A-Z0-9.]*STRONG\.SYS|ST\.E\.[A-Z0-9.]*STRONG\.SYS|CCTL)[A-Z0-9_.]*")
 counts = collections.OrderedDict(); fn = None
 for line in out.splitlines():
     m = re.search(r"Function : (\S+)", line)
