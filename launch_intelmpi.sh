@@ -1,31 +1,26 @@
 #!/bin/bash
-# Tensor-parallel forward benchmark, Intel MPI spelling of the launch line (ref launch_intelmpi.sh).
-# The I_MPI_* variables are kept for script compatibility; the dlbb launcher ignores them (there
-# is no shared-memory fabric to configure: ranks talk over NVLink).
+# TP forward benchmark of models.py, Intel MPI flavour of the command line (counterpart of the reference's
+# launch_intelmpi.sh): `-ppn`, `-genv K=V` and the I_MPI_* pinning variables.  bin/mpirun is the dlbb launcher;
+# it accepts the Hydra spelling and ignores I_MPI_FABRICS / I_MPI_SHM_LMT (ranks talk over NVLink, there is no
+# shared-memory fabric to tune) - they are exported only so that scripts which read them keep working.
+#
+#   WORLD_SIZE=8 ./launch_intelmpi.sh
+set -u
+here="$(cd "$(dirname "$0")" && pwd)"
+cd "$here"
+PATH="$here/bin:$PATH"
 
-cd "$(dirname "$0")"
-export PATH="$PWD/bin:$PATH"
+ranks="${WORLD_SIZE:-4}"
+cores="${CORES_PER_RANK:-14}"
+yaml="config/baseline_config.yaml"
 
-CONFIG_FILE="config/baseline_config.yaml"
-WORLD_SIZE=${WORLD_SIZE:-4}
-CORES_PER_RANK=${CORES_PER_RANK:-14}
+export OMP_NUM_THREADS="$cores" MKL_NUM_THREADS="$cores" OMP_NESTED=FALSE
+export I_MPI_PIN_DOMAIN=omp I_MPI_FABRICS=shm I_MPI_SHM_LMT=shm
 
-export OMP_NUM_THREADS=$CORES_PER_RANK
-export MKL_NUM_THREADS=$CORES_PER_RANK
-export OMP_NESTED=FALSE
-export I_MPI_PIN_DOMAIN=omp
-export I_MPI_FABRICS=shm
-export I_MPI_SHM_LMT=shm
-
-echo "Launching the IntelMPI-style run on $WORLD_SIZE rank(s)"
-mpirun -np $WORLD_SIZE \
-       -ppn $WORLD_SIZE \
-       -genv OMP_NUM_THREADS=$CORES_PER_RANK \
-       -genv MKL_NUM_THREADS=$CORES_PER_RANK \
-       -genv DLBB_WORLD_SIZE=$WORLD_SIZE \
-       python run_mpi.py \
-       --config $CONFIG_FILE \
-       --backend intelmpi || exit $?
-
-echo ""
-echo "IntelMPI experiment completed!"
+echo "run_mpi.py (backend label: intelmpi) on $ranks rank(s), $cores core(s) each"
+mpirun -np "$ranks" -ppn "$ranks" \
+       -genv OMP_NUM_THREADS="$cores" -genv MKL_NUM_THREADS="$cores" -genv DLBB_WORLD_SIZE="$ranks" \
+       python run_mpi.py --config "$yaml" --backend intelmpi
+rc=$?
+[ $rc -eq 0 ] && echo "done: results under the YAML's output_dir" || echo "run failed with exit code $rc"
+exit $rc

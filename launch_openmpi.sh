@@ -1,30 +1,27 @@
 #!/bin/bash
-# Tensor-parallel forward benchmark, Open MPI spelling of the launch line (ref launch_openmpi.sh).
-# `mpirun` here is bin/mpirun -> the dlbb launcher: same flags, one rank per B200, NUMA-aware core
-# binding.  WORLD_SIZE defaults to the YAML's 4; set it (1/2/4/8) to run on another GPU count.
+# TP forward benchmark of models.py, Open MPI flavour of the command line (counterpart of the reference's
+# launch_openmpi.sh).  bin/mpirun is the dlbb launcher: it takes Open MPI's flags, starts one rank per B200
+# and binds each rank to host cores near its GPU.
+#
+#   WORLD_SIZE=8 ./launch_openmpi.sh        ranks = GPUs (default: the YAML's world_size, 4)
+#   CORES_PER_RANK=8 ./launch_openmpi.sh    host cores per rank (default 14, as in the YAML)
+set -u
+here="$(cd "$(dirname "$0")" && pwd)"
+cd "$here"
+PATH="$here/bin:$PATH"
 
-cd "$(dirname "$0")"
-export PATH="$PWD/bin:$PATH"
+ranks="${WORLD_SIZE:-4}"
+cores="${CORES_PER_RANK:-14}"
+yaml="config/baseline_config.yaml"
 
-CONFIG_FILE="config/baseline_config.yaml"
-WORLD_SIZE=${WORLD_SIZE:-4}
-CORES_PER_RANK=${CORES_PER_RANK:-14}
+# host threading for the little CPU work that is left (data generation, statistics)
+export OMP_NUM_THREADS="$cores" MKL_NUM_THREADS="$cores" OMP_NESTED=FALSE
+export DLBB_WORLD_SIZE="$ranks"
 
-export OMP_NUM_THREADS=$CORES_PER_RANK
-export MKL_NUM_THREADS=$CORES_PER_RANK
-export OMP_NESTED=FALSE
-export DLBB_WORLD_SIZE=$WORLD_SIZE
-
-echo "Launching the OpenMPI-style run on $WORLD_SIZE rank(s)"
-mpirun -np $WORLD_SIZE \
-       --bind-to core \
-       --map-by socket:PE=$CORES_PER_RANK \
-       -x OMP_NUM_THREADS \
-       -x MKL_NUM_THREADS \
-       -x DLBB_WORLD_SIZE \
-       python run_mpi.py \
-       --config $CONFIG_FILE \
-       --backend openmpi || exit $?
-
-echo ""
-echo "OpenMPI experiment completed!"
+echo "run_mpi.py (backend label: openmpi) on $ranks rank(s), $cores core(s) each"
+mpirun -np "$ranks" --bind-to core --map-by "socket:PE=$cores" \
+       -x OMP_NUM_THREADS -x MKL_NUM_THREADS -x DLBB_WORLD_SIZE \
+       python run_mpi.py --config "$yaml" --backend openmpi
+rc=$?
+[ $rc -eq 0 ] && echo "done: results under the YAML's output_dir" || echo "run failed with exit code $rc"
+exit $rc
