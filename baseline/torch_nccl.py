@@ -56,12 +56,35 @@ class TorchTrainer:
         if world > 1:
             from torch.nn.parallel import DistributedDataParallel as DDP
             self.net = DDP(self.model, device_ids=[device.index], bucket_cap_mb=400, gradient_as_bucket_view=True)
-        self.opt = torch.optim.Adam(self.model.parameters(), lr=lr, fused=True)
+        # DLBB_TORCH_STATE=bf16 (default): torch.optim.Adam straight on the bf16 parameters - moments in bf16, no master
+        # copy (half the optimizer bytes of the native engine).  DLBB_TORCH_STATE=fp32: the native engine's contract in
+        # stock PyTorch - fp32 master weights and fp32 moments, stepped one layer at a time so that the fp32 copy of the
+        # gradients never exists for more than one layer (the whole model would not fit beside the activations).
+        import os
+        self.state = os.environ.get("DLBB_TORCH_STATE", "bf16")
+        if self.state == "fp32":
+            self.groups = []
+            mods = list(self.model.layers) + [self.model.ln_final]
+            for mod in mods:
+                ps = list(mod.parameters())
+                masters = [p.detach().float().clone() for p in ps]
+                self.groups.append((ps, masters, torch.optim.Adam(masters, lr=lr, fused=True)))
+        else:
+            self.opt = torch.optim.Adam(self.model.parameters(), lr=lr, fused=True)
 
     def step(self, x, target):
-        self.opt.zero_grad(set_to_none=True)
+        self.model.zero_grad(set_to_none=True)
         y = self.net(x)
         loss = F.mse_loss(y.float(), target.float())
         loss.backward()
-        self.opt.step()
+        if self.state == "fp32":
+            for ps, masters, opt in self.groups:
+                for p, m in zip(ps, masters):
+                    m.grad = p.grad.float()
+                opt.step()
+                torch._foreach_copy_(ps, masters)
+                for m in masters:
+                    m.grad = None
+        else:
+            self.opt.step()
         return loss.detach().reshape(1)

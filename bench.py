@@ -41,6 +41,7 @@ def parse_args():
     ap.add_argument("--seq", type=int, default=None)
     ap.add_argument("--layers", type=int, default=None, help="debug only: marks the result as reduced")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-collectives", action="store_true", help="skip the collective bus-bandwidth table (N > 1)")
     return ap.parse_args()
 
 
@@ -104,6 +105,66 @@ def reference_arm(args) -> None:
     print(json.dumps({"impl": "reference", "unavailable": why}))
 
 
+def collective_table(comm, dev, rank, world, barrier, max_over_ranks):
+    """Bus bandwidth of the native collectives next to NCCL on the same sizes, same process, same box: device-timed
+    tight loops (CUDA events around `iters` back-to-back calls after 3 warm-up calls), max over ranks.  `bytes` is the
+    size of the largest buffer of the call on one rank.  "ours": ordinary torch tensors; "ours_symm": tensors in
+    symmetric memory (SymmComm.alloc), which the NVLS kernels reduce / replicate in place.  NCCL is initialised here,
+    after the timed training loops."""
+    import torch
+    import torch.distributed as dist
+
+    if not dist.is_initialized():
+        dist.init_process_group("nccl", device_id=dev)
+    bf = torch.bfloat16
+    sizes = [1 << 10, 4 << 20, 128 << 20, 1 << 30]
+    arena_a, _ = comm.alloc(sizes[-1] // 2, bf)
+    arena_b, _ = comm.alloc(sizes[-1] // 2, bf)
+    busf = {"allreduce": 2.0 * (world - 1) / world, "allgather": (world - 1) / world, "reduce_scatter": (world - 1) / world,
+            "broadcast": 1.0, "alltoall": (world - 1) / world}
+
+    def timed(fn, iters):
+        for _ in range(3):
+            fn()
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(iters):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        return max_over_ranks(e0.elapsed_time(e1) / iters)
+
+    rows = []
+    for nbytes in sizes:
+        n = nbytes // 2 // (world * 8) * (world * 8)
+        iters = 20 if nbytes <= (4 << 20) else (8 if nbytes <= (128 << 20) else 4)
+        x, y = torch.ones(n, dtype=bf, device=dev), torch.empty(n, dtype=bf, device=dev)
+        xs, ys = arena_a[:n], arena_b[:n]
+        xs.fill_(1.0)
+        part, parts = y[:n // world], ys[:n // world]
+        arms = {
+            "allreduce": (lambda: comm.all_reduce(x), lambda: comm.all_reduce(xs), lambda: dist.all_reduce(x)),
+            "allgather": (lambda: comm.all_gather(x[:n // world], y), lambda: comm.all_gather(xs[:n // world], ys),
+                          lambda: dist.all_gather_into_tensor(y, x[:n // world])),
+            "reduce_scatter": (lambda: comm.reduce_scatter(x, part), lambda: comm.reduce_scatter(xs, parts),
+                               lambda: dist.reduce_scatter_tensor(part, x)),
+            "broadcast": (lambda: comm.broadcast(x, root=0), lambda: comm.broadcast(xs, root=0),
+                          lambda: dist.broadcast(x, src=0)),
+            "alltoall": (lambda: comm.all_to_all(x, y), lambda: comm.all_to_all(xs, ys),
+                         lambda: dist.all_to_all_single(y, x)),
+        }
+        for op, (ours, symm, nccl) in arms.items():
+            row = {"op": op, "bytes": n * 2}
+            for name, fn in (("ours", ours), ("ours_symm", symm), ("nccl", nccl)):
+                ms = timed(fn, iters)
+                row[f"{name}_us"] = round(ms * 1e3, 2)
+                row[f"{name}_busbw_gbs"] = round(n * 2 * busf[op] / ms / 1e6, 2)
+            rows.append(row)
+        del x, y
+    return {"dtype": "bf16", "timing": "CUDA events around back-to-back calls, max over ranks", "rows": rows}
+
+
 def main() -> None:
     args = parse_args()
     if args.impl == "reference":
@@ -129,9 +190,9 @@ def main() -> None:
         sys.exit(2)
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
-    if world > 1:
-        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        dist.init_process_group("nccl", device_id=dev)
+    os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+    if world > 1 and args.impl == "torch-nccl":
+        dist.init_process_group("nccl", device_id=dev)   # the library arm's data plane; ours never touches NCCL in the timed loops
 
     cfg = load_config(args.config)
     if args.model:
@@ -149,17 +210,28 @@ def main() -> None:
     backend = "torch-nccl" if args.impl == "torch-nccl" else "native"
     trainer = Trainer(cfg, device=dev, rank=rank, world_size=world, backend=backend)
 
+    comm = getattr(trainer, "comm", None)      # ours: the native communicator (symmetric memory, no NCCL)
+    if comm is not None:
+        sys.stderr.write(f"dlbb: comm up rank {rank}/{world} (multicast {'on' if comm.has_multicast else 'off'})\n")
+
     def barrier():
-        if world > 1:
-            dist.barrier()
         torch.cuda.synchronize()
+        if world > 1:
+            if comm is not None:
+                comm.host_barrier()
+            else:
+                dist.barrier()
+                torch.cuda.synchronize()
 
     def max_over_ranks(v: float) -> float:
         if world == 1:
             return v
-        t = torch.tensor([v], dtype=torch.float64, device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item())
+        t = torch.tensor([v, 0.0], dtype=torch.float64, device=dev)
+        if comm is not None:
+            comm.all_reduce(t, op="max")
+        else:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t[0].item())
 
     # ---------------- device-timed loop: batch resident, no host sync inside
     x_dev, t_dev = trainer.resident_batch()
@@ -199,9 +271,19 @@ def main() -> None:
                "api": "distributed_llm_backend_benchmark_b200.train.Trainer.fit", "last_loss": stats["last_loss"]}
     clocks = sampler.stop() if rank == 0 else None
 
+    # ---------------- second half of BASELINE.json's metric: collective bus bandwidth, ours next to NCCL
+    collectives = None
+    if world > 1 and comm is not None and not args.no_collectives:
+        try:
+            collectives = collective_table(comm, dev, rank, world, barrier, max_over_ranks)
+        except Exception as e:  # noqa: BLE001 - the headline number must survive a failure here
+            collectives = {"error": repr(e)}
+
     if rank == 0:
         mc = LLMConfig.from_dict(cfg)
         flops = 3.0 * mc.forward_flops(B * S)
+        flops_exec = trainer.flops_per_step() if hasattr(trainer, "flops_per_step") else flops
+        dense_qkv = args.impl != "ours" or trainer.engine.dense_qkv_backward
         out = {
             "metric": METRIC, "value": world * B / (ms / 1e3), "unit": "samples/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
@@ -210,17 +292,23 @@ def main() -> None:
             "config": {"model": f"models.py {cfg['model'].get('size', '?')} (H={mc.hidden_size}, L={mc.num_layers}, "
                                 f"F={mc.ffn_intermediate})",
                        "global_batch": world * B, "seq_len": S, "parallelism": f"dp{world}",
-                       "optimizer": "Adam (fp32 moments + fp32 master, bf16 params/grads)",
+                       "optimizer": ("Adam (fp32 moments + fp32 master, bf16 params/grads)" if args.impl == "ours" else
+                                     f"torch.optim.Adam fused, state {os.environ.get('DLBB_TORCH_STATE', 'bf16')}"),
+                       "qkv_backward": "dense" if dense_qkv else "sparse (structurally zero 2/3 of dW_qkv / dh1 skipped)",
                        "loss": "mse(ln_final(x_L), synthetic target)",
                        "l2": "per-step working set (>100 GB of weights, state and activations) is far larger "
                              "than the 126 MB L2, so no flush between iterations",
                        "baseline_metric": "DP samples/sec at 1/2/4/8 B200 (BASELINE.json); nothing published"},
             "tokens_per_s": world * B * S / (ms / 1e3),
+            "flops_executed": flops_exec,
+            "executed_tflops_per_gpu": flops_exec / (ms / 1e3) / 1e12,
+            "model_flops_3x_forward": flops,
             "model_tflops_per_gpu": flops / (ms / 1e3) / 1e12,
             "final_loss": final_loss,
             "gpu_launches": int(launches),
             "clocks": clocks,
             "e2e": e2e,
+            "collectives": collectives,
         }
         if reduced:
             out["INVALID"] = "reduced layer count (debug run)"
@@ -228,7 +316,7 @@ def main() -> None:
             out["INVALID"] = "optimizer skipped (debug run)"
         out["env"] = {k: v for k, v in os.environ.items() if k.startswith("DLBB_")}
         print(json.dumps(out), flush=True)
-    if world > 1:
+    if world > 1 and dist.is_initialized():
         dist.barrier()
         dist.destroy_process_group()
 

@@ -11,7 +11,7 @@
 
 namespace dlbb {
 
-constexpr int kMaxCtas = 160;         // channels: one signal-pad row per CTA of a collective kernel
+constexpr int kMaxCtas = 320;         // channels: one signal-pad row per CTA of a collective kernel (two CTAs per SM fit)
 constexpr int kPadStride = DLBB_MAX_RANKS;  // uint32 slots per row
 // Signal pad layout (uint32 words): [kMaxCtas rows][kPadStride] for kernel barriers, then
 // a second bank of the same shape for the fused DP kernel (it runs on a side stream concurrently
@@ -42,11 +42,15 @@ struct CommDev {
     char* stage_mc;       // multicast mapping of the staging segment (nullptr if unavailable)
     uint32_t* pads_mc;
     uint32_t* tile_flags[DLBB_MAX_RANKS];
+    long long watchdog_ns;   // device-side flag waits trap after this long (DLBB_WATCHDOG_SECONDS, default 60)
 };
 
 // The same logical user buffer on every rank, as mapped in this process (peer_registry.cpp).
+// `mc` is the NVLS multicast address of that buffer: only set when every rank's buffer sits at the same offset of
+// the same symmetric segment and that segment is bound to a multicast object (multimem.* may then be used on it).
 struct PeerView {
     char* ptr[DLBB_MAX_RANKS];
+    char* mc;
 };
 struct PeerRegistry;
 
@@ -58,6 +62,8 @@ PeerRegistry* peer_registry_create(dlbb_comm* c);
 void peer_registry_destroy(PeerRegistry* r);
 bool peer_registry_usable(const PeerRegistry* r);
 int peer_registry_resolve(dlbb_comm* c, PeerRegistry* r, const void* ptr, size_t bytes, PeerView* pv, bool* all_ok);
+// id of the live symmetric segment that holds [ptr, ptr + bytes) of this rank's memory, or -1
+int symm_segment_of(const dlbb_comm* c, const void* ptr, size_t bytes);
 }  // namespace dlbb
 
 struct dlbb_comm {

@@ -168,6 +168,9 @@ int try_multicast(dlbb_comm* c, dlbb::Segment& s) {
 }
 
 void fill_dev(dlbb_comm* c) {
+    const char* wd = getenv("DLBB_WATCHDOG_SECONDS");
+    const double wd_s = wd && atof(wd) > 0 ? atof(wd) : 60.0;
+    c->dev.watchdog_ns = static_cast<long long>(wd_s * 1e9);
     c->dev.rank = c->rank;
     c->dev.world = c->world;
     for (int p = 0; p < DLBB_MAX_RANKS; ++p) {

@@ -29,8 +29,9 @@ __device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
 }
 
 // Wait until *flag has reached `epoch` (monotonic, wrap-safe).  A peer that never arrives traps
-// after ~60 s instead of hanging the GPU (watchdog on device-side flag waits).
-__device__ __forceinline__ void wait_flag(const uint32_t* flag, uint32_t epoch, int peer) {
+// after `limit_ns` (CommDev::watchdog_ns: 60 s unless DLBB_WATCHDOG_SECONDS says otherwise) instead of
+// hanging the GPU (watchdog on device-side flag waits).  The message names the missing rank.
+__device__ __forceinline__ void wait_flag(const uint32_t* flag, uint32_t epoch, int peer, long long limit_ns) {
 #if DLBB_WATCHDOG
     long long t0 = 0;
     uint32_t it = 0;
@@ -41,9 +42,9 @@ __device__ __forceinline__ void wait_flag(const uint32_t* flag, uint32_t epoch, 
             long long now;
             asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
             if (t0 == 0) t0 = now;
-            else if (now - t0 > 60000000000ll) {
-                printf("dlbb: device barrier timeout: block %d waited 60 s for rank %d (epoch %u, flag %u)\n",
-                       blockIdx.x, peer, epoch, *flag);
+            else if (now - t0 > limit_ns) {
+                printf("dlbb: device barrier timeout: block %d waited %lld ms for rank %d (epoch %u, flag %u)\n",
+                       blockIdx.x, limit_ns / 1000000, peer, epoch, *flag);
                 __trap();
             }
         }
@@ -62,7 +63,7 @@ __device__ __forceinline__ void row_barrier(const CommDev& c, int bank, int row,
     if (threadIdx.x < c.world) {
         const int p = threadIdx.x;
         st_release_sys(pad_slot(c, p, bank, row, c.rank), epoch);
-        wait_flag(pad_slot(c, c.rank, bank, row, p), epoch, p);
+        wait_flag(pad_slot(c, c.rank, bank, row, p), epoch, p, c.watchdog_ns);
     }
     __syncthreads();
 }
@@ -74,7 +75,7 @@ __device__ __forceinline__ void grid_barrier(const CommDev& c, int bank, int nro
     if (threadIdx.x < c.world) st_release_sys(pad_slot(c, threadIdx.x, bank, blockIdx.x, c.rank), epoch);
     for (int i = threadIdx.x; i < nrows * c.world; i += blockDim.x) {
         const int row = i / c.world, p = i - row * c.world;
-        wait_flag(pad_slot(c, c.rank, bank, row, p), epoch, p);
+        wait_flag(pad_slot(c, c.rank, bank, row, p), epoch, p, c.watchdog_ns);
     }
     __syncthreads();
 }

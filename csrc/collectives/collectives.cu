@@ -178,7 +178,7 @@ broadcast_nvls_kernel(CommDev c, const char* __restrict__ src, char* __restrict_
             if (threadIdx.x < c.world && threadIdx.x != root)
                 st_release_sys(pad_slot(c, threadIdx.x, kBcFlagBank, row, root), flag_base + k + 1);
         } else {
-            if (threadIdx.x == 0) wait_flag(pad_slot(c, c.rank, kBcFlagBank, row, root), flag_base + k + 1, root);
+            if (threadIdx.x == 0) wait_flag(pad_slot(c, c.rank, kBcFlagBank, row, root), flag_base + k + 1, root, c.watchdog_ns);
             __syncthreads();
             if (dst_vec) {
                 for (int64_t i0 = c_lo + threadIdx.x; i0 < c_hi; i0 += (int64_t)blockDim.x * kU) {
@@ -623,7 +623,7 @@ allreduce_pipelined_kernel(CommDev c, const T* __restrict__ src, T* __restrict__
             if (t < c.world) st_release_sys(pad_slot(c, t, kPackBank, row, c.rank), base_pack + k + 1);
         } else if (role == 1) {
             // ---------------- REDUCE my share of the chunk
-            if (t < c.world) wait_flag(pad_slot(c, c.rank, kPackBank, row, t), base_pack + k + 1, t);
+            if (t < c.world) wait_flag(pad_slot(c, c.rank, kPackBank, row, t), base_pack + k + 1, t, c.watchdog_ns);
             group_bar_sync(2, kRedT);
             const int64_t share = (cnt + c.world - 1) / c.world;
             const int64_t s_lo = std::min<int64_t>(c_lo + c.rank * share, c_hi);
@@ -652,7 +652,7 @@ allreduce_pipelined_kernel(CommDev c, const T* __restrict__ src, T* __restrict__
             if (t < c.world) st_release_sys(pad_slot(c, t, kRedBank, row, c.rank), base_red + k + 1);
         } else {
             // ---------------- UNPACK
-            if (t < c.world) wait_flag(pad_slot(c, c.rank, kRedBank, row, t), base_red + k + 1, t);
+            if (t < c.world) wait_flag(pad_slot(c, c.rank, kRedBank, row, t), base_red + k + 1, t, c.watchdog_ns);
             group_bar_sync(3, kUnpackT);
             const uint4* my_out = reinterpret_cast<const uint4*>(c.stage[c.rank] + out_off);
             const bool dst_vec = (reinterpret_cast<uintptr_t>(dst) & 15) == 0 &&
@@ -739,7 +739,7 @@ chain_broadcast_kernel(CommDev c, const char* __restrict__ src, char* __restrict
     for (int k = 0; k < nchunks; ++k) {
         const int64_t c_lo = min(v_lo + (int64_t)k * kChainChunkVecs, v_hi), c_hi = min(c_lo + kChainChunkVecs, v_hi);
         if (!first) {
-            if (threadIdx.x == 0) wait_flag(pad_slot(c, c.rank, kChainBank, row, pred), flag_base + k + 1, pred);
+            if (threadIdx.x == 0) wait_flag(pad_slot(c, c.rank, kChainBank, row, pred), flag_base + k + 1, pred, c.watchdog_ns);
             __syncthreads();
         }
         for (int64_t i0 = c_lo + threadIdx.x; i0 < c_hi; i0 += (int64_t)blockDim.x * kU) {
@@ -792,7 +792,7 @@ chain_reduce_kernel(CommDev c, const T* __restrict__ src, T* __restrict__ dst, i
     for (int k = 0; k < nchunks; ++k) {
         const int64_t c_lo = min(v_lo + (int64_t)k * kChainChunkVecs, v_hi), c_hi = min(c_lo + kChainChunkVecs, v_hi);
         if (!first) {
-            if (threadIdx.x == 0) wait_flag(pad_slot(c, c.rank, kChainBank, row, pred), flag_base + k + 1, pred);
+            if (threadIdx.x == 0) wait_flag(pad_slot(c, c.rank, kChainBank, row, pred), flag_base + k + 1, pred, c.watchdog_ns);
             __syncthreads();
         }
         for (int64_t i0 = c_lo + threadIdx.x; i0 < c_hi; i0 += (int64_t)blockDim.x * kU) {
@@ -863,7 +863,7 @@ p2p_kernel(CommDev c, const char* __restrict__ send_src, int64_t send_bytes, int
     if (send_peer >= 0) {
         int64_t lo, hi;
         range(send_bytes, lo, hi);
-        if (threadIdx.x == 0) wait_flag(pad_slot(c, c.rank, kP2PBank, kP2PCtas + b, send_peer), send_epoch - 1, send_peer);
+        if (threadIdx.x == 0) wait_flag(pad_slot(c, c.rank, kP2PBank, kP2PCtas + b, send_peer), send_epoch - 1, send_peer, c.watchdog_ns);
         __syncthreads();
         cta_copy(c.stage[c.rank] + region_off + send_peer * slot_bytes + lo, send_src + lo, hi - lo, false);
         __syncthreads();
@@ -872,7 +872,7 @@ p2p_kernel(CommDev c, const char* __restrict__ send_src, int64_t send_bytes, int
     if (recv_peer >= 0) {
         int64_t lo, hi;
         range(recv_bytes, lo, hi);
-        if (threadIdx.x == 0) wait_flag(pad_slot(c, c.rank, kP2PBank, b, recv_peer), recv_epoch, recv_peer);
+        if (threadIdx.x == 0) wait_flag(pad_slot(c, c.rank, kP2PBank, b, recv_peer), recv_epoch, recv_peer, c.watchdog_ns);
         __syncthreads();
         cta_copy(recv_dst + lo, c.stage[recv_peer] + region_off + c.rank * slot_bytes + lo, hi - lo, true);
         __syncthreads();
@@ -928,6 +928,11 @@ static size_t dtype_size(int dt) {
 
 // CTAs of a zero-copy kernel: these only run for large messages, so take the full channel count.
 static int direct_ctas(const dlbb_comm* c) { return c->ctas > 0 ? std::min(c->ctas, kMaxCtas) : 128; }
+// ... scaled down for small messages (symmetric tensors take the direct kernels at every size): one CTA per 32 KiB
+static int direct_ctas(const dlbb_comm* c, int64_t bytes) {
+    if (c->ctas > 0) return std::min(c->ctas, kMaxCtas);
+    return static_cast<int>(std::min<int64_t>(128, std::max<int64_t>(1, bytes / (32 << 10))));
+}
 
 template <typename T, int OP>
 static int launch_reduce_T(dlbb_comm* c, const void* src, void* dst, const void* extra, const PieceList& pack,
@@ -995,7 +1000,7 @@ static int launch_twoshot_T(dlbb_comm* c, bool nvls, const void* src, void* dst,
         // (measured at 8 GPUs, 256 MiB: 631 GB/s busbw vs 515 for the phase-by-phase kernel and 646 for NCCL;
         // the peer-load variant does not profit - 362 vs 430 - and keeps the phase-by-phase kernel)
         constexpr int VE = 16 / sizeof(T);
-        const int ctas = c->ctas > 0 ? std::min(c->ctas, kMaxCtas) : 128;
+        const int ctas = c->ctas > 0 ? std::min(c->ctas, 148) : 128;   // one 512-thread CTA per SM: all rows must be resident
         const int64_t per = (n / VE + ctas - 1) / ctas;
         static const int kPipeChunkVecs = getenv("DLBB_PIPE_CHUNK_KB") ? atoi(getenv("DLBB_PIPE_CHUNK_KB")) * 64 : kPipeChunkVecsDefault;
         const uint32_t nchunks = static_cast<uint32_t>((per + kPipeChunkVecs - 1) / kPipeChunkVecs);
@@ -1079,9 +1084,15 @@ static int launch_move(dlbb_comm* c, const void* src, void* dst, const PieceList
 
 // Zero-copy gate shared by every collective: large enough, enabled, and every rank's buffer exportable.
 // Collective and host-blocking when it goes as far as the exchange (see peer_registry.cpp).
-static int try_zero_copy(dlbb_comm* c, const void* buf, int64_t bytes, int64_t gate_bytes, PeerView* pv, bool* ok) {
+// Tensors that live in a symmetric segment (SymmComm.alloc / symm_empty) take this path at every size: the peers have
+// them mapped already and, with a multicast mapping, the switch can reduce / replicate them in place.  `raw` is the
+// caller's pointer before any "not usable on this rank" substitution, so that all ranks decide alike (SPMD contract:
+// either every rank passes a symmetric tensor or none does).
+static int try_zero_copy(dlbb_comm* c, const void* buf, int64_t bytes, int64_t gate_bytes, PeerView* pv, bool* ok,
+                         const void* raw = nullptr) {
     *ok = false;
-    if (c->world == 1 || c->zero_copy_min == 0 || gate_bytes < (int64_t)c->zero_copy_min) return 0;
+    if (c->world == 1 || c->zero_copy_min == 0) return 0;
+    if (gate_bytes < (int64_t)c->zero_copy_min && symm_segment_of(c, raw ? raw : buf, static_cast<size_t>(bytes)) < 0) return 0;
     return peer_registry_resolve(c, c->reg, buf, static_cast<size_t>(bytes), pv, ok);
 }
 
@@ -1136,7 +1147,7 @@ static int64_t chain_min_bytes() {
 struct ChainGeom { int ctas; int nchunks; uint32_t flag_base; int64_t stage_off; uint32_t end_epoch; };
 static ChainGeom chain_geom(dlbb_comm* c, int64_t nvec, cudaStream_t s) {
     ChainGeom g;
-    g.ctas = c->ctas > 0 ? std::min(c->ctas, kMaxCtas) : 128;
+    g.ctas = c->ctas > 0 ? std::min(c->ctas, kMaxCtas) : 256;   // each CTA walks its chunks strictly in sequence: rows feed the pipeline
     const int64_t per = (nvec + g.ctas - 1) / g.ctas;
     g.nchunks = static_cast<int>(std::max<int64_t>(1, (per + kChainChunkVecs - 1) / kChainChunkVecs));
     g.flag_base = c->epoch[kChainBank];
@@ -1179,6 +1190,10 @@ static int launch_chain_reduce(dlbb_comm* c, int dtype, int op, const void* src,
     return -2;
 }
 
+}  // namespace dlbb
+#include "direct_kernels.cuh"
+namespace dlbb {
+
 static int allreduce_impl(dlbb_comm* c, const void* in, void* out, const void* extra, int64_t count, int dtype, int op,
                           int algo, const dlbb_view_t* in_view, cudaStream_t s) {
     const size_t es = dtype_size(dtype);
@@ -1207,12 +1222,40 @@ static int allreduce_impl(dlbb_comm* c, const void* in, void* out, const void* e
         bool zc = false;
         const int64_t gate = force_direct ? INT64_MAX : count * (int64_t)es;
         const bool mine_ok = in == out && (reinterpret_cast<uintptr_t>(out) & 15) == 0;
-        const int rc = try_zero_copy(c, mine_ok ? out : nullptr, count * (int64_t)es, gate, &pv, &zc);
+        const int rc = try_zero_copy(c, mine_ok ? out : nullptr, count * (int64_t)es, gate, &pv, &zc, out);
         if (rc) return rc;
         if (zc) {
             const int64_t n = count / (VE * c->world) * (VE * c->world);
             if (n > 0) {
-                const int rc2 = launch_allreduce_direct(c, dtype, op, pv, n, s);
+                int rc2;
+                if (pv.mc && nvls_ok && c->world > 2 - (int)env_flag("DLBB_MC_WORLD2", false) && env_flag("DLBB_MC_ALLREDUCE", true)) {
+                    // symmetric tensor with a multicast mapping: the switch reduces (multimem.ld_reduce) and
+                    // replicates (multimem.st) in place - every byte crosses each link about once per direction
+                    DirectPlan pl{};
+                    pl.mc_src = true;
+                    pl.sink = SINK_MC;
+                    pl.a.in = pv;
+                    pl.a.out_mc = pv.mc;
+                    const int64_t nv = n / VE, share = nv / c->world;
+                    pl.a.v_lo = c->rank * share;
+                    pl.a.v_hi = pl.a.v_lo + share;
+                    pl.a.out_shift = 0;
+                    rc2 = launch_direct(c, dtype, op, pl, s, n * (int64_t)es);
+                } else if (env_flag("DLBB_DIRECT_LEGACY", false)) {
+                    rc2 = launch_allreduce_direct(c, dtype, op, pv, n, s);
+                } else {
+                    // in place on everybody's tensor: rank r reduces its 1/P share and stores it into all of them
+                    DirectPlan pl{};
+                    pl.mc_src = false;
+                    pl.sink = SINK_ALL;
+                    pl.a.in = pv;
+                    pl.a.out = pv;
+                    const int64_t nv = n / VE, share = nv / c->world;
+                    pl.a.v_lo = c->rank * share;
+                    pl.a.v_hi = pl.a.v_lo + share;
+                    pl.a.out_shift = 0;
+                    rc2 = launch_direct(c, dtype, op, pl, s, n * (int64_t)es);
+                }
                 if (rc2) return rc2;
                 done = n;
             }
@@ -1277,6 +1320,41 @@ int dlbb_reduce(dlbb_comm_t* c, const void* in, void* out, int64_t count, int dt
     const int64_t VE = 16 / (int64_t)es;
     const bool nvls_ok = dlbb_comm_has_multicast(c) && op == DLBB_SUM &&
                          (dtype == DLBB_F16 || dtype == DLBB_BF16 || dtype == DLBB_F32);
+    if (c->world > 2 && c->world <= kDirectMaxWorld && (count * (int64_t)es) % 16 == 0 && count > 0 && env_flag("DLBB_REDUCE_DIRECT", true)) {
+        // Zero-copy, in place (what dist.reduce is): the non-root ranks each reduce 1/(P-1) of the message straight out
+        // of all ranks' tensors and store the result into the root's tensor - every link carries the message once in
+        // each direction and nothing is staged.  With a multicast mapping all P ranks reduce 1/P in the switch.
+        PeerView pv;
+        bool zc = false;
+        const int64_t bytes = count * (int64_t)es;
+        const bool mine_ok = aligned16(in) && in == out;
+        const int rc = try_zero_copy(c, mine_ok ? in : nullptr, bytes, bytes, &pv, &zc, in);
+        if (rc) return rc;
+        if (zc) {
+            const int64_t nv = bytes >> 4;
+            const bool use_mc = pv.mc && nvls_ok && env_flag("DLBB_MC_REDUCE", true);
+            if (bytes >= (int64_t)(1 << 20) * 4 && env_flag("DLBB_REDUCE_PULL", false))
+                return launch_reduce_pull(c, dtype, op, pv, out, nv, root, use_mc, static_cast<cudaStream_t>(stream));
+            // small messages: one hop - the reducers store their share straight into the root's tensor
+            DirectPlan pl{};
+            pl.mc_src = use_mc;
+            pl.sink = SINK_ONE;
+            pl.a.in = pv;
+            pl.a.out.ptr[0] = pv.ptr[root];
+            pl.a.out_shift = 0;
+            if (pl.mc_src) {
+                const int64_t share = (nv + c->world - 1) / c->world;
+                pl.a.v_lo = std::min<int64_t>(c->rank * share, nv);
+                pl.a.v_hi = std::min<int64_t>(pl.a.v_lo + share, nv);
+            } else if (c->rank != root) {
+                const int64_t j = (c->rank - root - 1 + c->world) % c->world;
+                const int64_t share = (nv + c->world - 2) / (c->world - 1);
+                pl.a.v_lo = std::min<int64_t>(j * share, nv);
+                pl.a.v_hi = std::min<int64_t>(pl.a.v_lo + share, nv);
+            }
+            return launch_direct(c, dtype, op, pl, static_cast<cudaStream_t>(stream), bytes);
+        }
+    }
     if (c->world > 2 && chain_min_bytes() > 0 && count * (int64_t)es >= chain_min_bytes()) {
         // Large message, several senders: pipelined chain ending at the root, every link carries the message once.
         const int64_t cap2 = static_cast<int64_t>(c->stage_bytes / es) / VE * VE;
@@ -1355,8 +1433,22 @@ int dlbb_reduce_scatter(dlbb_comm_t* c, const void* in, void* out, int64_t cpr, 
         bool zc = false;
         const int64_t total = cpr * (int64_t)es * c->world;
         const bool mine_ok = aligned16(in) && aligned16(out);
-        const int rc = try_zero_copy(c, mine_ok ? in : nullptr, total, total, &pv, &zc);
+        const int rc = try_zero_copy(c, mine_ok ? in : nullptr, total, total, &pv, &zc, in);
         if (rc) return rc;
+        if (zc && c->world <= kDirectMaxWorld) {
+            // all peers' loads of a vector in flight at once (or one multimem.ld_reduce on a symmetric input)
+            const bool nvls_ok = dlbb_comm_has_multicast(c) && op == DLBB_SUM &&
+                                 (dtype == DLBB_F16 || dtype == DLBB_BF16 || dtype == DLBB_F32);
+            DirectPlan pl{};
+            pl.mc_src = pv.mc && nvls_ok && env_flag("DLBB_MC_REDUCE_SCATTER", true);
+            pl.sink = SINK_ONE;
+            pl.a.in = pv;
+            pl.a.out.ptr[0] = static_cast<char*>(out);
+            pl.a.v_lo = (c->rank * cpr * (int64_t)es) >> 4;
+            pl.a.v_hi = pl.a.v_lo + ((cpr * (int64_t)es) >> 4);
+            pl.a.out_shift = pl.a.v_lo;
+            return launch_direct(c, dtype, op, pl, static_cast<cudaStream_t>(stream), total);
+        }
         if (zc)
             return launch_reduce(c, dtype, op, in, out, nullptr, PieceList{}, ViewDev{}, c->rank * cpr, cpr, total,
                                  static_cast<cudaStream_t>(stream), &pv);
@@ -1424,6 +1516,14 @@ int dlbb_broadcast(dlbb_comm_t* c, void* buf, int64_t count, int dtype, int root
     DLBB_REQUIRE(es != 0, "broadcast: unsupported dtype %d", dtype);
     DLBB_REQUIRE(root >= 0 && root < c->world, "broadcast: bad root %d", root);
     const int64_t total = count * es, cap = static_cast<int64_t>(c->stage_bytes) / 64 * 64;
+    if (c->world > 2 && c->world <= kDirectMaxWorld && total % 16 == 0 && total > 0 && env_flag("DLBB_BCAST_RELAY", true)) {
+        // Zero-copy relay (direct_kernels.cuh): the root's link carries the message once, nothing is staged.
+        PeerView pv;
+        bool zc = false;
+        const int rc = try_zero_copy(c, aligned16(buf) ? buf : nullptr, total, total, &pv, &zc, buf);
+        if (rc) return rc;
+        if (zc) return launch_bcast_relay(c, pv, total >> 4, root, static_cast<cudaStream_t>(stream));
+    }
     if (c->world > 2 && chain_min_bytes() > 0 && total >= chain_min_bytes()) {
         // Large message, several receivers: pipelined chain, every link carries the message once.
         for (int64_t done = 0; done < total; done += cap) {

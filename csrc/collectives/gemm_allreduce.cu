@@ -54,7 +54,7 @@ struct ArFusion {
             int m_blk, n_blk;
             tile_coords(t, num_m, num_n, group_m, m_blk, n_blk);
             const int m0 = m_blk * kBM, n0 = n_blk * bn;
-            if (rt < c.world) wait_flag(flag(c.rank, t, rt), epoch, rt);
+            if (rt < c.world) wait_flag(flag(c.rank, t, rt), epoch, rt, c.watchdog_ns);
             named_bar_sync(2, kRedThreads);
             const int rows = min(kBM, M - m0);
             const int vpr = min(bn, N - n0) >> 3;     // 16-byte vectors per tile row
