@@ -54,6 +54,23 @@ def test_gemm_cta_pair_matches_one_cta_bitwise(native_lib, ta, tb, shape):
     assert torch.equal(outs[0], outs[2]) and torch.equal(outs[1], outs[2])
 
 
+@pytest.mark.parametrize("ta", [False, True])
+@pytest.mark.parametrize("tb", [False, True])
+@pytest.mark.parametrize("shape", [(4096, 4096, 16384), (4096, 16384, 4096), (4096, 12288, 4096)])
+def test_gemm_model_shapes(native_lib, ta, tb, shape):
+    """The 7B model's shapes (K = 16384: the smem ring wraps 256 k-blocks; N = 4096: 256 pair tiles = 3.46 waves with a
+    partial last wave), all four operand majors, against fp32 torch.matmul on a 512-row slice spread over the M range
+    (the first rows, rows that straddle a tile edge, the last rows)."""
+    M, N, K = shape
+    a, b = _mk((K, M) if ta else (M, K), scale=0.25), _mk((N, K) if tb else (K, N), scale=0.25)
+    out = ops.matmul(a, b, transpose_a=ta, transpose_b=tb)
+    rows = torch.cat([torch.arange(0, 128), torch.arange(1984, 2240), torch.arange(M - 128, M)]).to(DEV)
+    A = (a.t() if ta else a)[rows].float()
+    ref = A @ (b.t() if tb else b).float()
+    assert relerr(out[rows], ref) < 6e-3
+    assert torch.isfinite(out.float()).all()
+
+
 @pytest.mark.parametrize("epi", ["gelu", "add", "mul_dgelu"])
 @pytest.mark.parametrize("shape", [(256, 512, 192), (200, 136, 72), (1024, 4096, 1024)])
 def test_gemm_epilogues(native_lib, epi, shape):
