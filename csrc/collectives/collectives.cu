@@ -881,6 +881,35 @@ p2p_kernel(CommDev c, const char* __restrict__ send_src, int64_t send_bytes, int
 }
 
 // ------------------------------------------------------------------------------------------
+// K13: bucket fusion.  Many small tensors, ONE launch: every tensor of the table is packed into its own 16 B aligned
+// slot of this rank's staging region, one barrier, then every rank reduces every slot across the ranks straight into
+// the tensors (one-shot form: these are small messages, launch and barrier latency is what fusion removes).
+// The analogue of oneCCL's CCL_FUSION (collectives/3d/launch_dsccl.sh:49-59); also what the DeepSpeed facade uses for
+// the gradients of a ZeRO-0 step (test/ds_mpi_test.py:36-47).
+constexpr int kMultiMax = 96;
+struct MultiTable {
+    int count;
+    void* buf[kMultiMax];          // in place: source and destination
+    int64_t n[kMultiMax];          // elements
+    int64_t off[kMultiMax];        // element offset of the slot inside the staging region (16 B aligned)
+};
+
+template <typename T, int OP>
+__global__ void __launch_bounds__(kCollThreads)
+reduce_multi_kernel(CommDev c, const __grid_constant__ MultiTable tb, int64_t stage_off, int bank, uint32_t epoch) {
+    const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t nth = (int64_t)gridDim.x * blockDim.x;
+    T* my_stage = reinterpret_cast<T*>(c.stage[c.rank] + stage_off);
+    const ViewDev dense{};
+    for (int t = 0; t < tb.count; ++t)
+        pack_typed<T>(my_stage + tb.off[t], static_cast<const T*>(tb.buf[t]), dense, 0, tb.n[t], tid, nth);
+    grid_barrier(c, bank, gridDim.x, epoch);
+    for (int t = 0; t < tb.count; ++t)
+        reduce_range<T, OP>(c, c.stage, static_cast<T*>(tb.buf[t]), nullptr, stage_off + tb.off[t] * (int64_t)sizeof(T), tb.n[t],
+                            tid, nth);
+}
+
+// ------------------------------------------------------------------------------------------
 // host side
 static int pick_ctas(const dlbb_comm* c, int64_t bytes) {
     int n = c->ctas;
@@ -1287,6 +1316,39 @@ static int allreduce_impl(dlbb_comm* c, const void* in, void* out, const void* e
         done += n;
     }
     return 0;
+}
+
+template <typename T, int OP>
+static int launch_multi_T(dlbb_comm* c, const MultiTable& tb, int64_t bytes, cudaStream_t s) {
+    const int ctas = pick_ctas(c, bytes);
+    const int64_t so = next_stage_off(c, s);
+    const uint32_t ep = ++c->epoch[0];
+    reduce_multi_kernel<T, OP><<<ctas, kCollThreads, 0, s>>>(c->dev, tb, so, 0, ep);
+    DLBB_CHECK_LAUNCH("reduce_multi_kernel");
+    return 0;
+}
+template <typename T>
+static int launch_multi_op(dlbb_comm* c, int op, const MultiTable& tb, int64_t bytes, cudaStream_t s) {
+    switch (op) {
+        case DLBB_SUM: return launch_multi_T<T, DLBB_SUM>(c, tb, bytes, s);
+        case DLBB_MAX: return launch_multi_T<T, DLBB_MAX>(c, tb, bytes, s);
+        case DLBB_MIN: return launch_multi_T<T, DLBB_MIN>(c, tb, bytes, s);
+        case DLBB_PROD: return launch_multi_T<T, DLBB_PROD>(c, tb, bytes, s);
+    }
+    set_error("unknown reduce op %d", op);
+    return -2;
+}
+static int launch_multi(dlbb_comm* c, int dtype, int op, const MultiTable& tb, int64_t bytes, cudaStream_t s) {
+    switch (dtype) {
+        case DLBB_F16: return launch_multi_op<__half>(c, op, tb, bytes, s);
+        case DLBB_BF16: return launch_multi_op<__nv_bfloat16>(c, op, tb, bytes, s);
+        case DLBB_F32: return launch_multi_op<float>(c, op, tb, bytes, s);
+        case DLBB_F64: return launch_multi_op<double>(c, op, tb, bytes, s);
+        case DLBB_I32: return launch_multi_op<int32_t>(c, op, tb, bytes, s);
+        case DLBB_I64: return launch_multi_op<int64_t>(c, op, tb, bytes, s);
+    }
+    set_error("reduction on unsupported dtype %d", dtype);
+    return -2;
 }
 
 }  // namespace dlbb
@@ -1722,6 +1784,48 @@ int dlbb_sendrecv(dlbb_comm_t* c, const void* send_buf, int64_t send_count, int 
         DLBB_CHECK_LAUNCH("p2p_kernel");
     }
     return 0;
+}
+
+int dlbb_allreduce_multi(dlbb_comm_t* c, void* const* bufs, const int64_t* counts, int n_tensors, int dtype, int op,
+                         void* stream) {
+    const int64_t es = (int64_t)dtype_size(dtype);
+    DLBB_REQUIRE(es != 0 && dtype != DLBB_U8, "allreduce_multi: unsupported dtype %d", dtype);
+    DLBB_REQUIRE(n_tensors >= 0, "allreduce_multi: negative tensor count");
+    // DLBB_FUSION=0: one collective per tensor; DLBB_FUSION_BYTES: the most a fused launch carries (default 16 MiB);
+    // a tensor above that size travels alone through the size-selected all-reduce.
+    static const bool fusion = env_flag("DLBB_FUSION", true);
+    static const int64_t fusion_bytes_env = getenv("DLBB_FUSION_BYTES") ? atoll(getenv("DLBB_FUSION_BYTES")) : (16ll << 20);
+    const int64_t limit = std::min<int64_t>(fusion_bytes_env, static_cast<int64_t>(c->stage_bytes));
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    MultiTable tb{};
+    int64_t used = 0;   // bytes of staging taken by the open bucket
+    auto flush = [&]() -> int {
+        if (tb.count == 0) return 0;
+        const int rc = launch_multi(c, dtype, op, tb, used, s);
+        tb.count = 0;
+        used = 0;
+        return rc;
+    };
+    for (int i = 0; i < n_tensors; ++i) {
+        const int64_t bytes = counts[i] * es;
+        if (counts[i] == 0) continue;
+        if (!fusion || bytes > limit || c->world == 1) {
+            const int rc = allreduce_impl(c, bufs[i], bufs[i], nullptr, counts[i], dtype, op, DLBB_ALGO_AUTO, nullptr, s);
+            if (rc) return rc;
+            continue;
+        }
+        const int64_t slot = (bytes + 15) / 16 * 16;
+        if (tb.count == kMultiMax || used + slot > limit) {
+            const int rc = flush();
+            if (rc) return rc;
+        }
+        tb.buf[tb.count] = bufs[i];
+        tb.n[tb.count] = counts[i];
+        tb.off[tb.count] = used / es;
+        ++tb.count;
+        used += slot;
+    }
+    return flush();
 }
 
 }  // extern "C"

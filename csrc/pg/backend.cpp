@@ -138,10 +138,26 @@ class BackendDlbb : public c10d::Backend {
     void set_oneshot_max_bytes(int64_t n) { dlbb_comm_set_oneshot_max_bytes(comm_, static_cast<size_t>(n)); }
     void set_algo(int a) { algo_ = a; }
 
+    // A tensor in symmetric memory (collective call: same sizes, same order on every rank).  Collectives on such
+    // tensors run in place on the peers' mappings at every size - multimem.ld_reduce / multimem.st where the box has
+    // NVLS - with no staging copy.  The memory belongs to the communicator and lives until it is shut down.
+    at::Tensor symm_empty(std::vector<int64_t> sizes, at::ScalarType dtype) {
+        int64_t numel = 1;
+        for (auto v : sizes) numel *= v;
+        const size_t bytes = static_cast<size_t>(std::max<int64_t>(numel, 1)) * c10::elementSize(dtype);
+        int seg = -1;
+        DLBB_CALL(dlbb_symm_alloc(comm_, bytes, &seg));
+        void* ptr = dlbb_symm_ptr(comm_, seg, getRank());
+        TORCH_CHECK(ptr != nullptr, "dlbb backend: symmetric allocation failed");
+        auto opts = at::TensorOptions().dtype(dtype).device(c10::Device(c10::kCUDA, dev_));
+        return at::from_blob(ptr, sizes, [](void*) {}, opts);
+    }
+
     // ------------------------------------------------------------------ collectives
     c10::intrusive_ptr<Work> allreduce(std::vector<at::Tensor>& tensors, const c10d::AllreduceOptions& opts) override {
         TORCH_CHECK(tensors.size() == 1, "dlbb backend: one tensor per rank");
         at::Tensor& t = tensors[0];
+        check_avg(opts.reduceOp, tensors);
         Staged s = stage_in(t, /*need_copy=*/true);
         const int dt = to_dlbb_dtype(s.dev.scalar_type(), true);
         if (s.dev.is_contiguous()) {
@@ -162,26 +178,40 @@ class BackendDlbb : public c10d::Backend {
         return finish(c10d::OpType::ALLREDUCE, s, {t});
     }
 
-    // Bucket fusion (the analogue of CCL_FUSION, collectives/3d/launch_dsccl.sh:49-59): many small tensors
-    // travel as one flat bucket -> one collective kernel instead of one per tensor.
+    // Bucket fusion (the analogue of CCL_FUSION, collectives/3d/launch_dsccl.sh:49-59): the tensors of one dtype travel
+    // as a pointer table to ONE multi-tensor kernel (pack, barrier, reduce, unpack - dlbb_allreduce_multi); nothing is
+    // concatenated or copied around it.  DLBB_FUSION=0 issues one collective per tensor, DLBB_FUSION_BYTES bounds a
+    // fused launch.  CPU tensors and strided views are brought to a dense device tensor first and copied back after.
     c10::intrusive_ptr<Work> allreduce_coalesced(std::vector<at::Tensor>& tensors,
                                                  const c10d::AllreduceCoalescedOptions& opts) override {
         TORCH_CHECK(!tensors.empty(), "dlbb backend: empty tensor list");
-        std::vector<at::Tensor> flat_parts;
-        flat_parts.reserve(tensors.size());
         c10::cuda::CUDAGuard g(dev_);
-        for (auto& t : tensors) flat_parts.push_back(t.to(c10::Device(c10::kCUDA, dev_)).reshape({-1}));
-        at::Tensor bucket = at::cat(flat_parts);
-        DLBB_CALL(dlbb_allreduce(comm_, bucket.data_ptr(), bucket.data_ptr(), bucket.numel(),
-                                 to_dlbb_dtype(bucket.scalar_type(), true), to_dlbb_op(opts.reduceOp), algo_, nullptr, stream()));
-        if (opts.reduceOp == c10d::ReduceOp::AVG) bucket.div_(getSize());
-        int64_t off = 0;
+        check_avg(opts.reduceOp, tensors);
+        std::vector<at::Tensor> work(tensors.size());
         bool any_cpu = false;
-        for (auto& t : tensors) {
-            t.copy_(bucket.narrow(0, off, t.numel()).view_as(t));
-            off += t.numel();
+        for (size_t i = 0; i < tensors.size(); ++i) {
+            const at::Tensor& t = tensors[i];
             any_cpu = any_cpu || !t.is_cuda();
+            work[i] = (t.is_cuda() && t.is_contiguous()) ? t : t.to(c10::Device(c10::kCUDA, dev_)).contiguous();
         }
+        std::vector<bool> taken(tensors.size(), false);
+        for (size_t i = 0; i < tensors.size(); ++i) {
+            if (taken[i]) continue;
+            const auto st = work[i].scalar_type();
+            std::vector<void*> ptrs;
+            std::vector<int64_t> counts;
+            for (size_t j = i; j < tensors.size(); ++j) {
+                if (taken[j] || work[j].scalar_type() != st) continue;
+                taken[j] = true;
+                ptrs.push_back(work[j].data_ptr());
+                counts.push_back(work[j].numel());
+            }
+            DLBB_CALL(dlbb_allreduce_multi(comm_, ptrs.data(), counts.data(), static_cast<int>(ptrs.size()),
+                                           to_dlbb_dtype(st, true), to_dlbb_op(opts.reduceOp), stream()));
+        }
+        if (opts.reduceOp == c10d::ReduceOp::AVG) at::_foreach_div_(work, static_cast<double>(getSize()));
+        for (size_t i = 0; i < tensors.size(); ++i)
+            if (!work[i].is_same(tensors[i])) tensors[i].copy_(work[i].view_as(tensors[i]));
         return done(c10d::OpType::ALLREDUCE_COALESCED, tensors, !any_cpu);
     }
 
@@ -198,6 +228,7 @@ class BackendDlbb : public c10d::Backend {
         TORCH_CHECK(tensors.size() == 1, "dlbb backend: one tensor per rank");
         at::Tensor& t = tensors[0];
         const int root = static_cast<int>(opts.rootRank);
+        check_avg(opts.reduceOp, tensors);
         Staged s = stage_in(t, true, true);
         DLBB_CALL(dlbb_reduce(comm_, s.dev.data_ptr(), s.dev.data_ptr(), s.dev.numel(),
                               to_dlbb_dtype(s.dev.scalar_type(), true), to_dlbb_op(opts.reduceOp), root, stream()));
@@ -266,6 +297,7 @@ class BackendDlbb : public c10d::Backend {
 
     c10::intrusive_ptr<Work> _reduce_scatter_base(at::Tensor& out, at::Tensor& in, const c10d::ReduceScatterOptions& opts) override {
         TORCH_CHECK(in.numel() == out.numel() * getSize(), "dlbb backend: reduce_scatter_tensor size mismatch");
+        check_avg(opts.reduceOp, {out});
         Staged si = stage_in(in, true, true);
         Staged so = stage_in(out, false, true);
         DLBB_CALL(dlbb_reduce_scatter(comm_, si.dev.data_ptr(), so.dev.data_ptr(), so.dev.numel(),
@@ -279,6 +311,7 @@ class BackendDlbb : public c10d::Backend {
         TORCH_CHECK(outs.size() == 1 && ins.size() == 1 && (int)ins[0].size() == getSize(),
                     "dlbb backend: reduce_scatter expects one output and world_size inputs");
         at::Tensor& out = outs[0];
+        check_avg(opts.reduceOp, outs);
         Staged so = stage_in(out, false, true);
         at::Tensor flat = at::empty({getSize(), out.numel()}, so.dev.options());
         for (int p = 0; p < getSize(); ++p) flat[p].copy_(ins[0][p].reshape({-1}));
@@ -332,6 +365,14 @@ class BackendDlbb : public c10d::Backend {
     }
 
   private:
+    // ReduceOp::AVG is SUM followed by a division: only meaningful on floating-point tensors
+    static void check_avg(const c10d::ReduceOp& op, const std::vector<at::Tensor>& ts) {
+        if (op != c10d::ReduceOp::AVG) return;
+        for (const auto& t : ts)
+            TORCH_CHECK(at::isFloatingType(t.scalar_type()), "dlbb backend: ReduceOp.AVG needs a floating-point tensor, got ",
+                        t.scalar_type());
+    }
+
     struct Staged {
         at::Tensor dev;        // tensor the kernel works on (the original if it already lives on the GPU)
         at::Tensor host;       // original CPU tensor (undefined for CUDA inputs)
@@ -444,7 +485,10 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
         .def("has_multicast", &BackendDlbb::has_multicast)
         .def("set_ctas", &BackendDlbb::set_ctas)
         .def("set_oneshot_max_bytes", &BackendDlbb::set_oneshot_max_bytes)
-        .def("set_algo", &BackendDlbb::set_algo);
+        .def("set_algo", &BackendDlbb::set_algo)
+        .def("symm_empty", [](BackendDlbb& b, std::vector<int64_t> sizes, py::object dtype) {
+            return b.symm_empty(std::move(sizes), torch::python::detail::py_object_to_dtype(dtype));
+        }, py::arg("sizes"), py::arg("dtype"));
     m.def(
         "create_backend",
         [](const c10::intrusive_ptr<c10d::Store>& store, int rank, int size, const std::chrono::milliseconds&) {

@@ -17,7 +17,11 @@ reference's host tensors, which the backend then stages through the GPU).
 Environment knobs: DLBB_SWEEP_DEVICE, DLBB_SWEEP_ITERS, DLBB_SWEEP_WARMUP,
 DLBB_SWEEP_OPS (comma list), DLBB_SWEEP_SIZES (1-D: comma list of labels or element counts),
 DLBB_SWEEP_MAX_MB (3-D: skip tensors above this size), DLBB_SWEEP_STRIDED=1 (3-D: communicate a
-non-contiguous [b,s,h] view, packed inside the kernel), DLBB_OUTPUT_DIR, DLBB_SKIP_EXISTING=1.
+non-contiguous [b,s,h] view, packed inside the kernel), DLBB_OUTPUT_DIR, DLBB_SKIP_EXISTING=1,
+DLBB_SWEEP_SYMMETRIC (default 1 on the native backend: the communicated tensors live in symmetric memory, which the
+NVLS / direct kernels work on in place; 0 = ordinary caching-allocator tensors), DLBB_SWEEP_TIGHT (default 1 on CUDA: after
+the reference-style loop the same call is also timed back to back between two CUDA events - ``device_tight_us`` - because
+the barrier-then-event bracket of the per-call measurement includes the host's time to enqueue the call on an idle GPU).
 """
 from __future__ import annotations
 
@@ -80,12 +84,27 @@ class _Clock:
 class TorchTransport:
     """deepspeed.comm / torch.distributed call sites (ref collectives/1d/dsccl.py:59-163)."""
 
-    def __init__(self, dist, rank, world, device):
+    def __init__(self, dist, rank, world, device, symmetric_alloc=None):
         self.d, self.rank, self.world, self.device = dist, rank, world, device
         self.clock = _Clock(device)
+        self.symm_alloc = symmetric_alloc          # callable(nbytes) -> uint8 tensor in symmetric memory, or None
+        self._arenas: dict[str, torch.Tensor] = {}
+        self.tight = device.type == "cuda" and os.environ.get("DLBB_SWEEP_TIGHT", "1") == "1"
 
     def barrier(self):
         self.d.barrier()
+
+    def buffer(self, role: str, like: torch.Tensor) -> torch.Tensor:
+        """A tensor shaped like `like`: in symmetric memory when the backend offers it (one growing arena per role,
+        allocated collectively - every rank asks for the same sizes in the same order), else an ordinary tensor."""
+        if self.symm_alloc is None:
+            return torch.empty_like(like, memory_format=torch.contiguous_format)
+        nbytes = like.numel() * like.element_size()
+        arena = self._arenas.get(role)
+        if arena is None or arena.numel() < nbytes:
+            arena = self.symm_alloc(max(nbytes, 2 * arena.numel() if arena is not None else 0, 1 << 21))
+            self._arenas[role] = arena
+        return arena[:nbytes].view(like.dtype).view(like.shape)
 
     def _loop(self, iterations, prepare, call):
         host, dev = [], []
@@ -95,20 +114,53 @@ class TorchTransport:
             h, dv = self.clock.measure(lambda: call(*args))
             host.append(h)
             dev.append(dv)
-        return host, (dev if dev and dev[0] is not None else None)
+        tight = None
+        if self.tight:
+            args = prepare()
+            for _ in range(2):
+                call(*args)
+            torch.cuda.synchronize(self.device)
+            self.barrier()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            n = max(4, min(iterations, 20))
+            e0.record()
+            for _ in range(n):
+                call(*args)
+            e1.record()
+            e1.synchronize()
+            tight = e0.elapsed_time(e1) / 1e3 / n
+        return host, (dev if dev and dev[0] is not None else None), tight
+
+    def _work_copy(self, data):
+        """The reference clones its input before every in-place call (outside the timed region); here the copy goes
+        into a persistent work buffer so that it can live in symmetric memory."""
+        if data.is_contiguous():
+            work = self.buffer("work", data)
+        else:
+            # keep the view's geometry: the work tensor is a view with the same sizes and strides over its own storage,
+            # so the backend sees the strided tensor (and packs / unpacks it inside the kernel), not a dense copy
+            span = 1 + sum((sz - 1) * st for sz, st in zip(data.shape, data.stride()))
+            flat = self.buffer("work", torch.empty(0, dtype=data.dtype, device=data.device).new_empty(span))
+            work = torch.as_strided(flat, data.shape, data.stride())
+
+        def prepare():
+            work.copy_(data)
+            return (work,)
+
+        return prepare
 
     def allreduce(self, data, iterations):
-        return self._loop(iterations, lambda: (data.clone(),), lambda t: self.d.all_reduce(t, op=self.d.ReduceOp.SUM))
+        return self._loop(iterations, self._work_copy(data), lambda t: self.d.all_reduce(t, op=self.d.ReduceOp.SUM))
 
     def allgather(self, data, iterations):
-        out = [torch.zeros_like(data) for _ in range(self.world)]
+        out = [torch.zeros_like(data, memory_format=torch.contiguous_format) for _ in range(self.world)]
         return self._loop(iterations, lambda: (), lambda: self.d.all_gather(out, data))
 
     def broadcast(self, data, iterations):
-        return self._loop(iterations, lambda: (data.clone(),), lambda t: self.d.broadcast(t, src=0))
+        return self._loop(iterations, self._work_copy(data), lambda t: self.d.broadcast(t, src=0))
 
     def gather(self, data, iterations):
-        out = [torch.zeros_like(data) for _ in range(self.world)] if self.rank == 0 else None
+        out = [torch.zeros_like(data, memory_format=torch.contiguous_format) for _ in range(self.world)] if self.rank == 0 else None
         return self._loop(iterations, lambda: (), lambda: self.d.gather(data, gather_list=out, dst=0))
 
     def scatter(self, data, iterations):
@@ -117,12 +169,14 @@ class TorchTransport:
         return self._loop(iterations, lambda: (), lambda: self.d.scatter(out, scatter_list=src, src=0))
 
     def reduce(self, data, iterations):
-        return self._loop(iterations, lambda: (data.clone(),), lambda t: self.d.reduce(t, dst=0, op=self.d.ReduceOp.SUM))
+        return self._loop(iterations, self._work_copy(data), lambda t: self.d.reduce(t, dst=0, op=self.d.ReduceOp.SUM))
 
     def reducescatter(self, data, iterations):
         n = data.numel() // self.world
-        out = torch.empty(n, dtype=data.dtype, device=data.device)
-        flat = data.reshape(-1)[:n * self.world]
+        flat_src = data.reshape(-1)[:n * self.world]
+        flat = self.buffer("work", flat_src)
+        flat.copy_(flat_src)
+        out = self.buffer("out", flat[:n])
         return self._loop(iterations, lambda: (), lambda: self.d.reduce_scatter_tensor(out, flat))
 
     def alltoall(self, data, iterations):
@@ -162,7 +216,7 @@ class MpiTransport:
             t0 = self.MPI.Wtime()
             call()
             host.append(self.MPI.Wtime() - t0)
-        return host, None
+        return host, None, None
 
     def allreduce(self, data, iterations):
         return self._loop(iterations, lambda: self.c.allreduce(data, op=self.MPI.SUM))
@@ -286,7 +340,22 @@ class _World:
             # bookkeeping collectives (timing gather, skip votes) use host tensors, except on backends
             # that only serve CUDA tensors (nccl)
             self.helper_device = self.device if spec.backend == "nccl" else torch.device("cpu")
-            self.transport = TorchTransport(dist, self.rank, self.world, self.device)
+            self.transport = TorchTransport(dist, self.rank, self.world, self.device, self._symmetric_allocator())
+
+    def _symmetric_allocator(self):
+        """`nbytes -> uint8 tensor` in the native backend's symmetric memory, or None (other backends, CPU tensors,
+        one rank, DLBB_SWEEP_SYMMETRIC=0)."""
+        if (self.device.type != "cuda" or self.world == 1 or self.spec.backend not in ("ccl", "dlbb")
+                or os.environ.get("DLBB_SWEEP_SYMMETRIC", "1") != "1"):
+            return None
+        try:
+            from ..parallel.backend import native_backend
+            be = native_backend()
+            if not hasattr(be, "symm_empty"):
+                return None
+            return lambda nbytes: be.symm_empty([int(nbytes)], torch.uint8)
+        except Exception:  # noqa: BLE001 - a Gloo fallback has no symmetric memory
+            return None
 
     def gather_timings(self, values):
         """[world][iters] on rank 0 (ref: comm.gather of lists / dist.gather of a float64 tensor)."""
@@ -333,19 +402,30 @@ def _run_config(w: _World, op: str, data, label: str):
     cannot desynchronise when only some of them fail."""
     fn = getattr(w.transport, op, None)
     err = None
-    host = dev = None
+    host = dev = tight = None
     try:
         if fn is None:
             raise NotImplementedError(f"operation {op!r} is not available for this flavour")
         fn(data, w.spec.warmup)
-        host, dev = fn(data, w.spec.iterations)
+        host, dev, tight = fn(data, w.spec.iterations)
     except Exception as e:  # noqa: BLE001
         err = e
     if w.any_failed(err is not None):
         if err is not None and w.rank == 0:
             print(f"  ERROR in {op} {label}: {err}  (configuration skipped on every rank)")
-        return None, None
-    return host, dev
+        return None, None, None
+    return host, dev, tight
+
+
+def _tight_fields(w: "_World", op: str, nbytes: int, tight) -> dict:
+    """Back-to-back device time of one call (max over ranks) and the bus bandwidth it gives."""
+    per_rank = w.gather_timings([tight]) if tight is not None else None
+    if w.rank != 0 or per_rank is None:
+        return {}
+    from ..utils.stats import bus_bandwidth
+    worst = max(v[0] for v in per_rank)
+    alg, bus = bus_bandwidth(op, w.world, nbytes, worst)
+    return {"device_tight_us": worst * 1e6, "algbw_tight_gbps": alg, "busbw_tight_gbps": bus}
 
 
 def _busbw(op, world, nbytes, dev_or_host):
@@ -384,10 +464,11 @@ def run_sweep_1d(spec: SweepSpec) -> None:
                 g = torch.Generator(device="cpu")
                 g.manual_seed(42 + w.rank)
                 data = torch.randn(n, dtype=torch.float16, generator=g).to(w.device)
-            host, dev = _run_config(w, op, data, size_name)
+            host, dev, tight = _run_config(w, op, data, size_name)
             if host is None:
                 continue
             all_host, all_dev = w.gather_timings(host), w.gather_timings(dev)
+            tight_fields = _tight_fields(w, op, n * 2, tight)
             if w.rank != 0:
                 continue
             med, alg, bus = _busbw(op, w.world, n * 2, all_dev or all_host)
@@ -402,9 +483,12 @@ def run_sweep_1d(spec: SweepSpec) -> None:
                           "warmup_iterations": spec.warmup, "measurement_iterations": spec.iterations,
                           "timing_method": "time.perf_counter()", "timings": all_host}
             result.update({"device": str(w.device), "element_size": 2, "timings_device": all_dev,
-                           "median_max_over_ranks_us": med * 1e6, "algbw_gbps": alg, "busbw_gbps": bus})
+                           "median_max_over_ranks_us": med * 1e6, "algbw_gbps": alg, "busbw_gbps": bus,
+                           "symmetric_memory": getattr(w.transport, "symm_alloc", None) is not None, **tight_fields})
             (out_dir / fname).write_text(json.dumps(result, indent=2))
-            print(f"  Saved: {fname}   median {med * 1e6:.1f} us   busbw {bus:.2f} GB/s")
+            print(f"  Saved: {fname}   median {med * 1e6:.1f} us   busbw {bus:.2f} GB/s"
+                  + (f"   back-to-back {tight_fields['device_tight_us']:.1f} us, {tight_fields['busbw_tight_gbps']:.2f} GB/s"
+                     if tight_fields else ""))
     if w.rank == 0:
         print("-" * 80)
         print(f"Benchmarking complete!  Results saved in '{spec.output_dir}/' directory")
@@ -448,14 +532,15 @@ def run_sweep_3d(spec: SweepSpec) -> None:
                     else:
                         tensor = torch.randn(b, s, h, dtype=torch.bfloat16, generator=g).to(w.device)
                     data = tensor.float().cpu().numpy() if spec.flavour == "mpi" else tensor
-                    host, dev = _run_config(w, op, data, f"({b},{s},{h})")
+                    host, dev, tight = _run_config(w, op, data, f"({b},{s},{h})")
                     if host is None:
                         continue
                     all_host, all_dev = w.gather_timings(host), w.gather_timings(dev)
+                    wire = nbytes * (2 if spec.flavour == "mpi" else 1)
+                    tight_fields = _tight_fields(w, op, wire, tight)
                     del tensor, data
                     if w.rank != 0:
                         continue
-                    wire = nbytes * (2 if spec.flavour == "mpi" else 1)
                     med, alg, bus = _busbw(op, w.world, wire, all_dev or all_host)
                     key = "mpi_implementation" if spec.flavour == "mpi" else "implementation"
                     result = {key: spec.implementation, "operation": op, "num_ranks": w.world,
@@ -469,9 +554,13 @@ def run_sweep_3d(spec: SweepSpec) -> None:
                     else:
                         result["backend"] = spec.backend
                     result.update({"device": str(w.device), "strided_view": strided, "timings_device": all_dev,
-                                   "median_max_over_ranks_us": med * 1e6, "algbw_gbps": alg, "busbw_gbps": bus})
+                                   "median_max_over_ranks_us": med * 1e6, "algbw_gbps": alg, "busbw_gbps": bus,
+                                   "symmetric_memory": getattr(w.transport, "symm_alloc", None) is not None and not strided,
+                                   **tight_fields})
                     (out_dir / fname).write_text(json.dumps(result, indent=2))
-                    print(f"  Saved: {fname}   median {med * 1e3:.3f} ms   busbw {bus:.2f} GB/s")
+                    print(f"  Saved: {fname}   median {med * 1e3:.3f} ms   busbw {bus:.2f} GB/s"
+                          + (f"   back-to-back {tight_fields['device_tight_us'] / 1e3:.3f} ms, "
+                             f"{tight_fields['busbw_tight_gbps']:.2f} GB/s" if tight_fields else ""))
     if w.rank == 0:
         print("-" * 80)
         print(f"Benchmarking complete!  Results saved in '{spec.output_dir}/' directory")

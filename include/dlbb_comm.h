@@ -86,6 +86,12 @@ typedef struct {
  * inside the kernel) unless stated otherwise.  in/out may alias where the op allows in-place. */
 int dlbb_allreduce(dlbb_comm_t* c, const void* in, void* out, int64_t count, int dtype, int op,
                    int algo, const dlbb_view_t* in_view, void* stream);
+/* Bucket fusion (K13; the analogue of CCL_FUSION, collectives/3d/launch_dsccl.sh:49-59): all-reduce `n_tensors` tensors
+ * of one dtype in place with as few launches as possible - up to 96 tensors / DLBB_FUSION_BYTES (default 16 MiB) per
+ * launch are packed, reduced and unpacked by ONE kernel; larger tensors go through dlbb_allreduce one by one.
+ * DLBB_FUSION=0 switches fusion off (one collective per tensor). */
+int dlbb_allreduce_multi(dlbb_comm_t* c, void* const* bufs, const int64_t* counts, int n_tensors, int dtype,
+                         int op, void* stream);
 /* out = sum over ranks(in) + residual (bf16, SUM): the TP row-parallel reduction fused with the
  * residual add (K16 without the GEMM; ref models.py:95 + :173/:188). */
 int dlbb_allreduce_residual_bf16(dlbb_comm_t* c, const void* in, const void* residual, void* out,
