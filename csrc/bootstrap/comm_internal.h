@@ -83,6 +83,8 @@ struct dlbb_comm {
     int default_algo = 0;          // DLBB_ALGO: what DLBB_ALGO_AUTO resolves to (0 = size-based choice)
     dlbb::PeerRegistry* reg = nullptr;   // zero-copy access to the peers' ordinary allocations
     size_t zero_copy_min = 0;      // messages of at least this many bytes try the zero-copy kernels (0 = never)
+    const dlbb_view_t* out_view = nullptr;   // set by the *_v entry points for the duration of one call: strided destination
+    int64_t out_base = 0;                    // ... and the logical element offset of the launch being issued inside it
     bool debug_poison = false;     // DLBB_DEBUG_POISON=1: 0xFF-fill a staging region before the kernel that rewrites it
     dlbb::CommDev dev{};
 };

@@ -26,6 +26,7 @@ struct ViewDev {
     int ndim;            // 0 = contiguous
     int64_t size[4];
     int64_t stride[4];
+    int64_t base;        // logical element offset added to every index (a launch that covers a later part of the view)
 };
 
 struct Piece {           // a contiguous run of elements / bytes
@@ -42,6 +43,7 @@ struct PieceList {
 
 __device__ __forceinline__ int64_t view_offset(const ViewDev& v, int64_t idx) {
     if (v.ndim == 0) return idx;
+    idx += v.base;
     int64_t off = 0;
 #pragma unroll
     for (int d = 3; d >= 0; --d) {
@@ -52,6 +54,30 @@ __device__ __forceinline__ int64_t view_offset(const ViewDev& v, int64_t idx) {
         }
     }
     return off;
+}
+
+// A strided destination (K12, unpack side): can 16-byte vectors of T be stored with one index decomposition each?
+// (innermost dimension dense and a whole number of vectors, every other stride and the base pointer vector aligned)
+template <typename T>
+__device__ __forceinline__ bool view_vec_ok(const ViewDev& v, const void* base) {
+    constexpr int VE = 16 / sizeof(T);
+    if (v.ndim == 0) return (reinterpret_cast<uintptr_t>(base) & 15) == 0;
+    const int last = v.ndim - 1;
+    bool ok = v.stride[last] == 1 && v.size[last] % VE == 0 && v.base % VE == 0 && (reinterpret_cast<uintptr_t>(base) & 15) == 0;
+    for (int d = 0; d < last; ++d) ok = ok && (v.stride[d] % VE == 0);
+    return ok;
+}
+// Store vector i (elements [i*VE, (i+1)*VE) of the logical, dense order) into a dense or strided destination.
+template <typename T>
+__device__ __forceinline__ void store_view_vec(T* __restrict__ dst, const ViewDev& v, int64_t i, const uint4& o, bool vec_ok) {
+    constexpr int VE = 16 / sizeof(T);
+    if (vec_ok) {
+        st_v4(dst + view_offset(v, i * VE), o);
+    } else {
+        const T* ot = reinterpret_cast<const T*>(&o);
+#pragma unroll
+        for (int e = 0; e < VE; ++e) dst[view_offset(v, i * VE + e)] = ot[e];
+    }
 }
 
 // Copy `bytes` bytes with the whole grid.  16-byte vectors when everything is aligned.
@@ -78,6 +104,51 @@ __device__ __forceinline__ void grid_copy_bytes(char* dst, const char* src, int6
     }
 }
 
+// ---- byte-typed view access for the data-movement kernels (element size known only at run time)
+__device__ __forceinline__ int64_t view_byte_off(const ViewDev& v, int es, int64_t b) {   // logical byte -> byte in the view
+    if (v.ndim == 0) return b;
+    const int64_t e = b / es;
+    return view_offset(v, e) * es + (b - e * es);
+}
+__device__ __forceinline__ bool view_vec_ok_bytes(const ViewDev& v, int es, const void* base) {
+    if ((reinterpret_cast<uintptr_t>(base) & 15) != 0) return false;
+    if (v.ndim == 0) return true;
+    if (es > 16 || 16 % es != 0) return false;
+    const int VE = 16 / es, last = v.ndim - 1;
+    bool ok = v.stride[last] == 1 && v.size[last] % VE == 0;
+    for (int d = 0; d < last; ++d) ok = ok && (v.stride[d] % VE == 0);
+    return ok;
+}
+// 16 logical bytes starting at logical byte offset b (a multiple of 16) of a dense or strided local buffer
+__device__ __forceinline__ uint4 ld_view_v4(const char* base, const ViewDev& v, int es, int64_t b, bool vec_ok) {
+    if (vec_ok) return ld_stream_v4(base + view_byte_off(v, es, b));
+    uint4 r;
+    char* rb = reinterpret_cast<char*>(&r);
+#pragma unroll
+    for (int k = 0; k < 16; ++k) rb[k] = base[view_byte_off(v, es, b + k)];
+    return r;
+}
+__device__ __forceinline__ void st_view_v4(char* base, const ViewDev& v, int es, int64_t b, const uint4& val, bool vec_ok) {
+    if (vec_ok) { st_v4(base + view_byte_off(v, es, b), val); return; }
+    const char* vb = reinterpret_cast<const char*>(&val);
+#pragma unroll
+    for (int k = 0; k < 16; ++k) base[view_byte_off(v, es, b + k)] = vb[k];
+}
+// Whole grid: copy `bytes` logical bytes from a peer's (dense) staging into a strided local destination, starting at
+// logical byte offset b0 of the view.
+__device__ __forceinline__ void grid_scatter_view(char* dst, const ViewDev& ov, int es, int64_t b0, const char* src, int64_t bytes) {
+    const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t nth = (int64_t)gridDim.x * blockDim.x;
+    const bool vec = view_vec_ok_bytes(ov, es, dst) && (b0 & 15) == 0 && (reinterpret_cast<uintptr_t>(src) & 15) == 0;
+    int64_t done = 0;
+    if (vec) {
+        const int64_t nvec = bytes >> 4;
+        for (int64_t i = tid; i < nvec; i += nth) st_v4(dst + view_byte_off(ov, es, b0 + (i << 4)), ld_peer_v4(src + (i << 4)));
+        done = nvec << 4;
+    }
+    for (int64_t b = done + tid; b < bytes; b += nth) dst[view_byte_off(ov, es, b0 + b)] = ld_peer_scalar(src + b);
+}
+
 // ------------------------------------------------------------------------------------------
 // K1: barrier
 __global__ void barrier_kernel(CommDev c, int bank, uint32_t epoch) { row_barrier(c, bank, blockIdx.x, epoch); }
@@ -90,7 +161,8 @@ __global__ void barrier_kernel(CommDev c, int bank, uint32_t epoch) { row_barrie
 // stream from overwriting the source - until all peers have read it.  CTA b only meets CTA b of the peers.
 __global__ void __launch_bounds__(kCollThreads)
 move_kernel(CommDev c, const char* __restrict__ src, char* __restrict__ dst, PieceList pack, PieceList pull,
-            ViewDev view, int elem_size, int64_t stage_off, int bank, uint32_t epoch, const __grid_constant__ PeerView pv, int direct) {
+            ViewDev view, int elem_size, int64_t stage_off, int bank, uint32_t epoch, const __grid_constant__ PeerView pv, int direct,
+            ViewDev oview) {
     if (direct) {
         row_barrier(c, bank, blockIdx.x, epoch);   // the peers' kernels run, so their sources are final
         for (int i = 0; i < pull.count; ++i) {
@@ -124,7 +196,8 @@ move_kernel(CommDev c, const char* __restrict__ src, char* __restrict__ dst, Pie
     grid_barrier(c, bank, gridDim.x, epoch);
     for (int i = 0; i < pull.count; ++i) {
         const Piece& pc = pull.p[i];
-        grid_copy_bytes<true>(dst + pc.b_off, c.stage[pc.peer] + stage_off + pc.a_off, pc.n);
+        if (oview.ndim == 0) grid_copy_bytes<true>(dst + pc.b_off, c.stage[pc.peer] + stage_off + pc.a_off, pc.n);
+        else grid_scatter_view(dst, oview, elem_size, pc.b_off, c.stage[pc.peer] + stage_off + pc.a_off, pc.n);   // unpack in-kernel
     }
 }
 
@@ -138,7 +211,8 @@ constexpr int kBcFlagBank = 4;        // one-directional "chunk k is in your sta
 
 __global__ void __launch_bounds__(kCollThreads)
 broadcast_nvls_kernel(CommDev c, const char* __restrict__ src, char* __restrict__ dst, int64_t bytes, int root,
-                      int64_t stage_off, uint32_t flag_base, int nchunks, int bank, uint32_t end_epoch) {
+                      int64_t stage_off, uint32_t flag_base, int nchunks, int bank, uint32_t end_epoch, ViewDev view, int es,
+                      int64_t b0) {   // b0: logical byte offset of this launch inside the view (strided tensors only)
     const int64_t nvec = bytes >> 4;
     const int64_t per = (nvec + gridDim.x - 1) / gridDim.x;
     const int64_t v_lo = std::min<int64_t>((int64_t)blockIdx.x * per, nvec);
@@ -146,13 +220,17 @@ broadcast_nvls_kernel(CommDev c, const char* __restrict__ src, char* __restrict_
     const int64_t tail_lo = nvec << 4;   // < 16 trailing bytes travel with chunk 0 of CTA 0 as plain peer stores
     const int row = blockIdx.x;
     const char* mine = c.stage[c.rank] + stage_off;
-    const bool src_vec = (reinterpret_cast<uintptr_t>(src) & 15) == 0, dst_vec = (reinterpret_cast<uintptr_t>(dst) & 15) == 0;
+    // (a strided tensor - the same view on every rank - is gathered by the root and scattered by the receivers here)
+    const bool src_vec = view_vec_ok_bytes(view, es, src), dst_vec = view_vec_ok_bytes(view, es, dst);
     for (int k = 0; k < nchunks; ++k) {
         const int64_t c_lo = std::min<int64_t>(v_lo + (int64_t)k * kBcChunkVecs, v_hi);
         const int64_t c_hi = std::min<int64_t>(c_lo + kBcChunkVecs, v_hi);
         if (c.rank == root) {
             char* mc = c.stage_mc + stage_off;
-            if (src_vec) {
+            if (view.ndim != 0) {
+                for (int64_t i = c_lo + threadIdx.x; i < c_hi; i += blockDim.x)
+                    mm_st_v4(mc + (i << 4), ld_view_v4(src, view, es, b0 + (i << 4), src_vec && (b0 & 15) == 0));
+            } else if (src_vec) {
                 for (int64_t i0 = c_lo + threadIdx.x; i0 < c_hi; i0 += (int64_t)blockDim.x * kU) {
                     uint4 v[kU];
 #pragma unroll
@@ -173,14 +251,17 @@ broadcast_nvls_kernel(CommDev c, const char* __restrict__ src, char* __restrict_
             }
             if (row == 0 && k == 0)
                 for (int64_t b = tail_lo + threadIdx.x; b < bytes; b += blockDim.x)
-                    for (int p = 0; p < c.world; ++p) c.stage[p][stage_off + b] = src[b];
+                    for (int p = 0; p < c.world; ++p) c.stage[p][stage_off + b] = src[view_byte_off(view, es, b0 + b)];
             __syncthreads();
             if (threadIdx.x < c.world && threadIdx.x != root)
                 st_release_sys(pad_slot(c, threadIdx.x, kBcFlagBank, row, root), flag_base + k + 1);
         } else {
             if (threadIdx.x == 0) wait_flag(pad_slot(c, c.rank, kBcFlagBank, row, root), flag_base + k + 1, root, c.watchdog_ns);
             __syncthreads();
-            if (dst_vec) {
+            if (view.ndim != 0) {
+                for (int64_t i = c_lo + threadIdx.x; i < c_hi; i += blockDim.x)
+                    st_view_v4(dst, view, es, b0 + (i << 4), ld_peer_v4(mine + (i << 4)), dst_vec && (b0 & 15) == 0);
+            } else if (dst_vec) {
                 for (int64_t i0 = c_lo + threadIdx.x; i0 < c_hi; i0 += (int64_t)blockDim.x * kU) {
                     uint4 v[kU];
 #pragma unroll
@@ -194,7 +275,7 @@ broadcast_nvls_kernel(CommDev c, const char* __restrict__ src, char* __restrict_
                 for (int64_t b = (c_lo << 4) + threadIdx.x; b < (c_hi << 4); b += blockDim.x) dst[b] = ld_peer_scalar(mine + b);
             }
             if (row == 0 && k == 0)
-                for (int64_t b = tail_lo + threadIdx.x; b < bytes; b += blockDim.x) dst[b] = ld_peer_scalar(mine + b);
+                for (int64_t b = tail_lo + threadIdx.x; b < bytes; b += blockDim.x) dst[view_byte_off(view, es, b0 + b)] = ld_peer_scalar(mine + b);
         }
     }
     // The root never waits inside the loop; this closing barrier keeps it from running ahead and reusing the
@@ -302,9 +383,28 @@ __device__ __forceinline__ typename Acc<T>::type reduce_scalar(const CommDev& c,
 template <typename T, int OP>
 __device__ __forceinline__ void reduce_range(const CommDev& c, char* const (&bases)[DLBB_MAX_RANKS], T* __restrict__ dst,
                                              const T* __restrict__ extra, int64_t base_b, int64_t red_n, int64_t tid,
-                                             int64_t nth) {
+                                             int64_t nth, const ViewDev& ov = ViewDev{}) {
     constexpr int VE = 16 / sizeof(T);
     using A = typename Acc<T>::type;
+    if (ov.ndim != 0) {
+        // strided destination: element i of the reduced range lands at dst[view_offset(ov, i)] (no `extra` here)
+        const bool ovec = view_vec_ok<T>(ov, dst) && (base_b & 15) == 0;
+        int64_t done_v = 0;
+        if (ovec) {
+            const int64_t nvec = red_n / VE;
+            for (int64_t i0 = tid; i0 < nvec; i0 += nth * kU) {
+                uint4 o[kU];
+                reduce_batch<T, OP>(c, bases, base_b, i0, nth, nvec, o);
+#pragma unroll
+                for (int u = 0; u < kU; ++u)
+                    if (i0 + u * nth < nvec) store_view_vec<T>(dst, ov, i0 + u * nth, o[u], true);
+            }
+            done_v = nvec * VE;
+        }
+        for (int64_t i = done_v + tid; i < red_n; i += nth)
+            dst[view_offset(ov, i)] = from_acc<T>(reduce_scalar<T, OP>(c, bases, base_b + i * (int64_t)sizeof(T)));
+        return;
+    }
     const bool vec_ok = (base_b & 15) == 0 && (reinterpret_cast<uintptr_t>(dst) & 15) == 0 &&
                         (extra == nullptr || (reinterpret_cast<uintptr_t>(extra) & 15) == 0);
     int64_t done = 0;
@@ -347,7 +447,7 @@ template <typename T, int OP>
 __global__ void __launch_bounds__(kCollThreads)
 reduce_kernel(CommDev c, const T* __restrict__ src, T* __restrict__ dst, const T* __restrict__ extra, PieceList pack,
               ViewDev view, int64_t red_off, int64_t red_n, int64_t stage_off, int bank, uint32_t epoch,
-              const __grid_constant__ PeerView pv, int direct) {
+              const __grid_constant__ PeerView pv, int direct, ViewDev oview) {
     const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const int64_t nth = (int64_t)gridDim.x * blockDim.x;
     if (direct) {
@@ -361,7 +461,7 @@ reduce_kernel(CommDev c, const T* __restrict__ src, T* __restrict__ dst, const T
     const int64_t red_b = red_off * (int64_t)sizeof(T);
     if (red_n > 0) {
         if (direct) reduce_range<T, OP>(c, pv.ptr, dst, extra, red_b, red_n, tid, nth);
-        else reduce_range<T, OP>(c, c.stage, dst, extra, stage_off + red_b, red_n, tid, nth);
+        else reduce_range<T, OP>(c, c.stage, dst, extra, stage_off + red_b, red_n, tid, nth, oview);
     }
     if (direct) row_barrier(c, bank, blockIdx.x, epoch + 1);
 }
@@ -477,7 +577,7 @@ template <typename T, int OP, bool NVLS>
 __global__ void __launch_bounds__(kCollThreads)
 allreduce_twoshot_kernel(CommDev c, const T* __restrict__ src, T* __restrict__ dst, const T* __restrict__ extra,
                          ViewDev view, int64_t src_off, int64_t n, int64_t in_off, int64_t out_off, int bank,
-                         uint32_t epoch, int root) {
+                         uint32_t epoch, int root, ViewDev oview) {
     constexpr int VE = 16 / sizeof(T);
     using A = typename Acc<T>::type;
     // range of this CTA, in vectors; n is a multiple of VE * world (host pads the tail separately)
@@ -502,8 +602,11 @@ allreduce_twoshot_kernel(CommDev c, const T* __restrict__ src, T* __restrict__ d
                     for (int u = 0; u < kUR; ++u)
                         if (i0 + u * blockDim.x < v_hi) o[u] = MmReduce<T>::ld(c.stage_mc + in_off + ((i0 + u * blockDim.x) << 4));
 #pragma unroll
-                    for (int u = 0; u < kUR; ++u)
-                        if (i0 + u * blockDim.x < v_hi) store_result_vec<T>(dst, extra, i0 + u * blockDim.x, o[u], dv);
+                    for (int u = 0; u < kUR; ++u) {
+                        if (i0 + u * blockDim.x >= v_hi) continue;
+                        if (oview.ndim != 0) store_view_vec<T>(dst, oview, i0 + u * blockDim.x, o[u], view_vec_ok<T>(oview, dst));
+                        else store_result_vec<T>(dst, extra, i0 + u * blockDim.x, o[u], dv);
+                    }
                 }
             }
             row_barrier(c, bank, blockIdx.x, epoch + 1);   // nobody repacks this staging region before the root is done
@@ -549,6 +652,7 @@ allreduce_twoshot_kernel(CommDev c, const T* __restrict__ src, T* __restrict__ d
     const uint4* my_out = reinterpret_cast<const uint4*>(c.stage[c.rank] + out_off);
     const bool dst_vec = (reinterpret_cast<uintptr_t>(dst) & 15) == 0 &&
                          (extra == nullptr || (reinterpret_cast<uintptr_t>(extra) & 15) == 0);
+    const bool ovec = view_vec_ok<T>(oview, dst);   // strided destination: scatter by the view (no `extra` then)
     for (int64_t i0 = v_lo + threadIdx.x; i0 < v_hi; i0 += (int64_t)blockDim.x * kU) {
         uint4 ob[kU];
 #pragma unroll
@@ -571,7 +675,9 @@ allreduce_twoshot_kernel(CommDev c, const T* __restrict__ src, T* __restrict__ d
                     for (int e = 0; e < VE; ++e) ot[e] = from_acc<T>(to_acc<T>(ot[e]) + to_acc<T>(extra[i * VE + e]));
                 }
             }
-            if (dst_vec) {
+            if (oview.ndim != 0) {
+                store_view_vec<T>(dst, oview, i, o, ovec);
+            } else if (dst_vec) {
                 st_v4(reinterpret_cast<uint4*>(dst) + i, o);
             } else {
                 const T* ot = reinterpret_cast<const T*>(&o);
@@ -601,7 +707,7 @@ template <typename T, int OP, bool NVLS>
 __global__ void __launch_bounds__(kPipeThreads, 1)
 allreduce_pipelined_kernel(CommDev c, const T* __restrict__ src, T* __restrict__ dst, const T* __restrict__ extra,
                            ViewDev view, int64_t src_off, int64_t n, int64_t in_off, int64_t out_off, uint32_t base_pack,
-                           uint32_t base_red, int kPipeChunkVecs) {
+                           uint32_t base_red, int kPipeChunkVecs, ViewDev oview) {
     constexpr int VE = 16 / sizeof(T);
     const int64_t nvec = n / VE;
     const int64_t per = (nvec + gridDim.x - 1) / gridDim.x;
@@ -672,7 +778,9 @@ allreduce_pipelined_kernel(CommDev c, const T* __restrict__ src, T* __restrict__
 #pragma unroll
                         for (int e = 0; e < VE; ++e) ot[e] = from_acc<T>(to_acc<T>(ot[e]) + to_acc<T>(extra[i * VE + e]));
                     }
-                    if (dst_vec) {
+                    if (oview.ndim != 0) {
+                        store_view_vec<T>(dst, oview, i, o, view_vec_ok<T>(oview, dst));
+                    } else if (dst_vec) {
                         st_v4(reinterpret_cast<uint4*>(dst) + i, o);
                     } else {
                         const T* ot = reinterpret_cast<const T*>(&o);
@@ -945,6 +1053,13 @@ static ViewDev make_view(const dlbb_view_t* v) {
     return d;
 }
 
+// The strided destination of the running *_v call (comm_internal.h: out_view / out_base), for the kernels' unpack side.
+static ViewDev out_view_of(const dlbb_comm* c) {
+    ViewDev v = out_view_of(c);
+    v.base = c->out_view ? c->out_base : 0;
+    return v;
+}
+
 static size_t dtype_size(int dt) {
     switch (dt) {
         case DLBB_F16: case DLBB_BF16: return 2;
@@ -972,7 +1087,7 @@ static int launch_reduce_T(dlbb_comm* c, const void* src, void* dst, const void*
         c->epoch[0] += 2;
         reduce_kernel<T, OP><<<direct_ctas(c), kCollThreads, 0, s>>>(
             c->dev, static_cast<const T*>(src), static_cast<T*>(dst), static_cast<const T*>(extra), pack, view, red_off,
-            red_n, 0, 0, ep, *direct, 1);
+            red_n, 0, 0, ep, *direct, 1, ViewDev{});
         DLBB_CHECK_LAUNCH("reduce_kernel (zero-copy)");
         return 0;
     }
@@ -981,7 +1096,7 @@ static int launch_reduce_T(dlbb_comm* c, const void* src, void* dst, const void*
     const uint32_t ep = ++c->epoch[0];
     reduce_kernel<T, OP><<<ctas, kCollThreads, 0, s>>>(c->dev, static_cast<const T*>(src), static_cast<T*>(dst),
                                                        static_cast<const T*>(extra), pack, view, red_off, red_n, so, 0,
-                                                       ep, PeerView{}, 0);
+                                                       ep, PeerView{}, 0, out_view_of(c));
     DLBB_CHECK_LAUNCH("reduce_kernel");
     return 0;
 }
@@ -1039,11 +1154,11 @@ static int launch_twoshot_T(dlbb_comm* c, bool nvls, const void* src, void* dst,
         if (use_nvls)
             allreduce_pipelined_kernel<T, OP, true><<<ctas, kPipeThreads, 0, s>>>(
                 c->dev, static_cast<const T*>(src), static_cast<T*>(dst), static_cast<const T*>(extra), view, src_off, n,
-                in_off, out_off, bp, br, kPipeChunkVecs);
+                in_off, out_off, bp, br, kPipeChunkVecs, out_view_of(c));
         else
             allreduce_pipelined_kernel<T, OP, false><<<ctas, kPipeThreads, 0, s>>>(
                 c->dev, static_cast<const T*>(src), static_cast<T*>(dst), static_cast<const T*>(extra), view, src_off, n,
-                in_off, out_off, bp, br, kPipeChunkVecs);
+                in_off, out_off, bp, br, kPipeChunkVecs, out_view_of(c));
         DLBB_CHECK_LAUNCH("allreduce_pipelined_kernel");
         return 0;
     }
@@ -1054,11 +1169,11 @@ static int launch_twoshot_T(dlbb_comm* c, bool nvls, const void* src, void* dst,
     if (use_nvls)
         allreduce_twoshot_kernel<T, OP, true><<<ctas, kCollThreads, 0, s>>>(
             c->dev, static_cast<const T*>(src), static_cast<T*>(dst), static_cast<const T*>(extra), view, src_off, n,
-            in_off, out_off, 0, ep, root);
+            in_off, out_off, 0, ep, root, out_view_of(c));
     else
         allreduce_twoshot_kernel<T, OP, false><<<ctas, kCollThreads, 0, s>>>(
             c->dev, static_cast<const T*>(src), static_cast<T*>(dst), static_cast<const T*>(extra), view, src_off, n,
-            in_off, out_off, 0, ep, root);
+            in_off, out_off, 0, ep, root, out_view_of(c));
     DLBB_CHECK_LAUNCH("allreduce_twoshot_kernel");
     return 0;
 }
@@ -1098,7 +1213,7 @@ static int launch_move(dlbb_comm* c, const void* src, void* dst, const PieceList
         const uint32_t ep = c->epoch[0] + 1;
         c->epoch[0] += 2;
         move_kernel<<<direct_ctas(c), kCollThreads, 0, s>>>(c->dev, static_cast<const char*>(src), static_cast<char*>(dst),
-                                                            pack, pull, view, elem_size, 0, 0, ep, *direct, 1);
+                                                            pack, pull, view, elem_size, 0, 0, ep, *direct, 1, ViewDev{});
         DLBB_CHECK_LAUNCH("move_kernel (zero-copy)");
         return 0;
     }
@@ -1106,7 +1221,7 @@ static int launch_move(dlbb_comm* c, const void* src, void* dst, const PieceList
     const int64_t so = next_stage_off(c, s);
     const uint32_t ep = ++c->epoch[0];
     move_kernel<<<ctas, kCollThreads, 0, s>>>(c->dev, static_cast<const char*>(src), static_cast<char*>(dst), pack, pull,
-                                              view, elem_size, so, 0, ep, PeerView{}, 0);
+                                              view, elem_size, so, 0, ep, PeerView{}, 0, out_view_of(c));
     DLBB_CHECK_LAUNCH("move_kernel");
     return 0;
 }
@@ -1301,7 +1416,8 @@ static int allreduce_impl(dlbb_comm* c, const void* in, void* out, const void* e
             if (n == 0) { oneshot = true; n = std::min(left, cap); }
         }
         const char* ext = extra ? static_cast<const char*>(extra) + done * es : nullptr;
-        char* o = static_cast<char*>(out) + done * es;
+        char* o = static_cast<char*>(out) + (c->out_view ? 0 : done * es);   // a strided output is addressed through its view
+        c->out_base = done;
         int rc;
         if (oneshot) {
             PieceList pack{};
@@ -1369,6 +1485,20 @@ int dlbb_allreduce(dlbb_comm_t* c, const void* in, void* out, int64_t count, int
     return allreduce_impl(c, in, out, nullptr, count, dtype, op, algo, in_view, static_cast<cudaStream_t>(stream));
 }
 
+int dlbb_allreduce_v(dlbb_comm_t* c, const void* in, void* out, int64_t count, int dtype, int op, int algo,
+                     const dlbb_view_t* in_view, const dlbb_view_t* out_view, void* stream) {
+    // a strided destination keeps the call on the staged kernels, whose unpack phase scatters by the view
+    c->out_view = (out_view && out_view->ndim > 0) ? out_view : nullptr;
+    static const dlbb_view_t kDense1 = {1, {0, 0, 0, 0}, {1, 0, 0, 0}};
+    dlbb_view_t dense = kDense1;
+    dense.size[0] = count;
+    // (zero-copy needs dense tensors on both sides: a 1-D dense descriptor for the input switches it off as well)
+    const dlbb_view_t* iv = (in_view && in_view->ndim > 0) ? in_view : (c->out_view ? &dense : nullptr);
+    const int rc = allreduce_impl(c, in, out, nullptr, count, dtype, op, algo, iv, static_cast<cudaStream_t>(stream));
+    c->out_view = nullptr;
+    return rc;
+}
+
 int dlbb_allreduce_residual_bf16(dlbb_comm_t* c, const void* in, const void* residual, void* out, int64_t count,
                                  void* stream) {
     return allreduce_impl(c, in, out, residual, count, DLBB_BF16, DLBB_SUM, DLBB_ALGO_AUTO, nullptr,
@@ -1376,7 +1506,55 @@ int dlbb_allreduce_residual_bf16(dlbb_comm_t* c, const void* in, const void* res
 }
 
 int dlbb_reduce(dlbb_comm_t* c, const void* in, void* out, int64_t count, int dtype, int op, int root, void* stream) {
+    return dlbb_reduce_v(c, in, out, count, dtype, op, root, nullptr, nullptr, stream);
+}
+
+// Strided tensors (K12): the input view is gathered by the pack phase, the root's output view is scattered by the
+// store / unpack phase of the same kernel.  Views keep the call on the staged kernels.
+static int reduce_views(dlbb_comm_t* c, const void* in, void* out, int64_t count, int dtype, int op, int root,
+                        const ViewDev& view, cudaStream_t s) {
     const size_t es = dtype_size(dtype);
+    const int64_t VE = 16 / (int64_t)es;
+    const bool nvls_ok = dlbb_comm_has_multicast(c) && op == DLBB_SUM && (dtype == DLBB_F16 || dtype == DLBB_BF16 || dtype == DLBB_F32);
+    int64_t done = 0;
+    if (c->world > 2) {
+        const int64_t unit = VE * c->world;
+        const int64_t cap2 = static_cast<int64_t>(c->stage_bytes / es) / unit * unit;
+        while (count - done >= unit) {
+            const int64_t n = std::min(count - done, cap2) / unit * unit;
+            c->out_base = done;
+            const int rc = launch_twoshot(c, dtype, op, nvls_ok, in, static_cast<char*>(out) + (c->out_view ? 0 : done * es), nullptr, view, done, n, s, root);
+            if (rc) return rc;
+            done += n;
+        }
+    }
+    if (done < count) {
+        const int64_t cap = static_cast<int64_t>(c->stage_bytes / es);
+        for (; done < count; done += cap) {
+            const int64_t n = std::min(cap, count - done);
+            c->out_base = done;
+            PieceList pack{};
+            pack.count = 1;
+            pack.p[0] = Piece{0, done, 0, n};
+            const int rc = launch_reduce(c, dtype, op, in, static_cast<char*>(out) + (c->out_view ? 0 : done * es), nullptr, pack, view, 0,
+                                         c->rank == root ? n : 0, n * es, s);
+            if (rc) return rc;
+        }
+    }
+    return 0;
+}
+
+int dlbb_reduce_v(dlbb_comm_t* c, const void* in, void* out, int64_t count, int dtype, int op, int root,
+                  const dlbb_view_t* in_view, const dlbb_view_t* out_view, void* stream) {
+    const size_t es = dtype_size(dtype);
+    if ((in_view && in_view->ndim > 0) || (out_view && out_view->ndim > 0)) {
+        DLBB_REQUIRE(es != 0 && dtype != DLBB_U8, "reduce: unsupported dtype %d", dtype);
+        DLBB_REQUIRE(root >= 0 && root < c->world, "reduce: bad root %d", root);
+        c->out_view = (out_view && out_view->ndim > 0) ? out_view : nullptr;
+        const int rc = reduce_views(c, in, out, count, dtype, op, root, make_view(in_view), static_cast<cudaStream_t>(stream));
+        c->out_view = nullptr;
+        return rc;
+    }
     DLBB_REQUIRE(es != 0 && dtype != DLBB_U8, "reduce: unsupported dtype %d", dtype);
     DLBB_REQUIRE(root >= 0 && root < c->world, "reduce: bad root %d", root);
     const int64_t VE = 16 / (int64_t)es;
@@ -1573,25 +1751,27 @@ int dlbb_allgather(dlbb_comm_t* c, const void* in, void* out, int64_t cpr, int d
     return 0;
 }
 
-int dlbb_broadcast(dlbb_comm_t* c, void* buf, int64_t count, int dtype, int root, void* stream) {
+int dlbb_broadcast_v(dlbb_comm_t* c, void* buf, int64_t count, int dtype, int root, const dlbb_view_t* buf_view, void* stream) {
     const int64_t es = (int64_t)dtype_size(dtype);
     DLBB_REQUIRE(es != 0, "broadcast: unsupported dtype %d", dtype);
     DLBB_REQUIRE(root >= 0 && root < c->world, "broadcast: bad root %d", root);
+    const ViewDev view = make_view(buf_view);   // strided tensor (same geometry on every rank): packed / unpacked in-kernel
     const int64_t total = count * es, cap = static_cast<int64_t>(c->stage_bytes) / 64 * 64;
-    if (c->world > 2 && c->world <= kDirectMaxWorld && total % 16 == 0 && total > 0 && env_flag("DLBB_BCAST_RELAY", true)) {
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    if (view.ndim == 0 && c->world > 2 && c->world <= kDirectMaxWorld && total % 16 == 0 && total > 0 && env_flag("DLBB_BCAST_RELAY", true)) {
         // Zero-copy relay (direct_kernels.cuh): the root's link carries the message once, nothing is staged.
         PeerView pv;
         bool zc = false;
         const int rc = try_zero_copy(c, aligned16(buf) ? buf : nullptr, total, total, &pv, &zc, buf);
         if (rc) return rc;
-        if (zc) return launch_bcast_relay(c, pv, total >> 4, root, static_cast<cudaStream_t>(stream));
+        if (zc) return launch_bcast_relay(c, pv, total >> 4, root, s);
     }
-    if (c->world > 2 && chain_min_bytes() > 0 && total >= chain_min_bytes()) {
+    if (view.ndim == 0 && c->world > 2 && chain_min_bytes() > 0 && total >= chain_min_bytes()) {
         // Large message, several receivers: pipelined chain, every link carries the message once.
         for (int64_t done = 0; done < total; done += cap) {
             const int64_t n = std::min(cap, total - done);
-            const ChainGeom g = chain_geom(c, n >> 4, static_cast<cudaStream_t>(stream));
-            chain_broadcast_kernel<<<g.ctas, kCollThreads, 0, static_cast<cudaStream_t>(stream)>>>(
+            const ChainGeom g = chain_geom(c, n >> 4, s);
+            chain_broadcast_kernel<<<g.ctas, kCollThreads, 0, s>>>(
                 c->dev, static_cast<const char*>(buf) + done, static_cast<char*>(buf) + done, n, root, g.stage_off,
                 g.flag_base, g.nchunks, g.end_epoch);
             DLBB_CHECK_LAUNCH("chain_broadcast_kernel");
@@ -1606,19 +1786,21 @@ int dlbb_broadcast(dlbb_comm_t* c, void* buf, int64_t count, int dtype, int root
             const int ctas = c->ctas > 0 ? std::min(c->ctas, kMaxCtas)
                                          : static_cast<int>(std::min<int64_t>(128, std::max<int64_t>(1, n / (64 << 10))));
             // (not poisoned: the root may multicast into a receiver's staging before that receiver has entered the kernel)
-            const int64_t so = next_stage_off(c, static_cast<cudaStream_t>(stream), false);
+            const int64_t so = next_stage_off(c, s, false);
             const int64_t per = ((n >> 4) + ctas - 1) / ctas;
             const int nchunks = static_cast<int>(std::max<int64_t>(1, (per + kBcChunkVecs - 1) / kBcChunkVecs));
             const uint32_t fb = c->epoch[kBcFlagBank];
             c->epoch[kBcFlagBank] += nchunks;
             const uint32_t ep = ++c->epoch[0];
-            broadcast_nvls_kernel<<<ctas, kCollThreads, 0, static_cast<cudaStream_t>(stream)>>>(
-                c->dev, static_cast<const char*>(buf) + done, static_cast<char*>(buf) + done, n, root, so, fb, nchunks, 0, ep);
+            const int64_t ptr_off = view.ndim ? 0 : done;   // a strided tensor is addressed through the view from its base
+            broadcast_nvls_kernel<<<ctas, kCollThreads, 0, s>>>(
+                c->dev, static_cast<const char*>(buf) + ptr_off, static_cast<char*>(buf) + ptr_off, n, root, so, fb, nchunks, 0, ep,
+                view, (int)es, view.ndim ? done : 0);
             DLBB_CHECK_LAUNCH("broadcast_nvls_kernel");
         }
         return 0;
     }
-    {   // zero-copy: everyone pulls from the root's tensor
+    if (view.ndim == 0) {   // zero-copy: everyone pulls from the root's tensor
         PeerView pv;
         bool zc = false;
         const int rc = try_zero_copy(c, buf, total, total, &pv, &zc);
@@ -1626,27 +1808,39 @@ int dlbb_broadcast(dlbb_comm_t* c, void* buf, int64_t count, int dtype, int root
         if (zc) {
             PieceList pull{};
             if (c->rank != root) { pull.count = 1; pull.p[0] = Piece{root, 0, 0, total}; }
-            return launch_move(c, buf, buf, PieceList{}, pull, ViewDev{}, (int)es, total, static_cast<cudaStream_t>(stream),
-                               &pv);
+            return launch_move(c, buf, buf, PieceList{}, pull, ViewDev{}, (int)es, total, s, &pv);
         }
     }
-    for (int64_t done = 0; done < total; done += cap) {
+    c->out_view = buf_view;   // receivers scatter into the view inside the kernel
+    c->out_base = 0;
+    int rc = 0;
+    for (int64_t done = 0; done < total && rc == 0; done += cap) {
         const int64_t n = std::min(cap, total - done);
         PieceList pack{}, pull{};
         if (c->rank == root) { pack.count = 1; pack.p[0] = Piece{0, done, 0, n}; }
         else { pull.count = 1; pull.p[0] = Piece{root, 0, done, n}; }
-        const int rc = launch_move(c, buf, buf, pack, pull, ViewDev{}, (int)es, n, static_cast<cudaStream_t>(stream));
-        if (rc) return rc;
+        rc = launch_move(c, buf, buf, pack, pull, view, (int)es, n, s);
     }
-    return 0;
+    c->out_view = nullptr;
+    return rc;
+}
+
+int dlbb_broadcast(dlbb_comm_t* c, void* buf, int64_t count, int dtype, int root, void* stream) {
+    return dlbb_broadcast_v(c, buf, count, dtype, root, nullptr, stream);
 }
 
 int dlbb_gather(dlbb_comm_t* c, const void* in, void* out, int64_t count, int dtype, int root, void* stream) {
+    return dlbb_gather_v(c, in, out, count, dtype, root, nullptr, stream);
+}
+
+int dlbb_gather_v(dlbb_comm_t* c, const void* in, void* out, int64_t count, int dtype, int root, const dlbb_view_t* in_view,
+                  void* stream) {
     const int64_t es = (int64_t)dtype_size(dtype);
     DLBB_REQUIRE(es != 0, "gather: unsupported dtype %d", dtype);
     DLBB_REQUIRE(root >= 0 && root < c->world, "gather: bad root %d", root);
     const int64_t total = count * es, cap = static_cast<int64_t>(c->stage_bytes) / 64 * 64;
-    {   // zero-copy: the root pulls every rank's input tensor
+    const ViewDev gview = make_view(in_view);   // strided input: gathered by the pack phase of the kernel
+    if (gview.ndim == 0) {   // zero-copy: the root pulls every rank's input tensor
         PeerView pv;
         bool zc = false;
         const bool mine_ok = c->rank != root || in == static_cast<char*>(out) + root * total ||
@@ -1672,7 +1866,7 @@ int dlbb_gather(dlbb_comm_t* c, const void* in, void* out, int64_t count, int dt
             pull.count = c->world;
             for (int p = 0; p < c->world; ++p) pull.p[p] = Piece{p, 0, p * total + done, n};
         }
-        const int rc = launch_move(c, in, out, pack, pull, ViewDev{}, (int)es, n * c->world, static_cast<cudaStream_t>(stream));
+        const int rc = launch_move(c, in, out, pack, pull, gview, (int)es, n * c->world, static_cast<cudaStream_t>(stream));
         if (rc) return rc;
     }
     return 0;

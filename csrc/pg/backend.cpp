@@ -109,6 +109,32 @@ static int to_dlbb_op(const c10d::ReduceOp& op) {
     return DLBB_SUM;
 }
 
+// Data-movement ops only need the element size: pick any dtype of that size.
+static int move_dtype(int64_t elem_size) {
+    switch (elem_size) {
+        case 1: return DLBB_U8;
+        case 2: return DLBB_F16;
+        case 4: return DLBB_F32;
+        case 8: return DLBB_F64;
+        default: return -1;
+    }
+}
+
+// Descriptor of a non-contiguous tensor for in-kernel packing / unpacking (K12).  False when the tensor has more than
+// four dimensions, zero or negative strides or an element size the kernels do not move as a unit: the caller then makes
+// a dense copy.
+static bool strided_view(const at::Tensor& t, dlbb_view_t* v) {
+    if (t.dim() == 0 || t.dim() > 4 || move_dtype(t.element_size()) < 0) return false;
+    v->ndim = static_cast<int>(t.dim());
+    for (int i = 0; i < 4; ++i) { v->size[i] = 0; v->stride[i] = 0; }
+    for (int i = 0; i < v->ndim; ++i) {
+        if (t.stride(i) <= 0 && t.size(i) > 1) return false;
+        v->size[i] = t.size(i);
+        v->stride[i] = t.stride(i);
+    }
+    return true;
+}
+
 class BackendDlbb : public c10d::Backend {
   public:
     BackendDlbb(const c10::intrusive_ptr<c10d::Store>& store, int rank, int size) : Backend(rank, size) {
@@ -169,10 +195,9 @@ class BackendDlbb : public c10d::Backend {
             dlbb_view_t v{};
             v.ndim = static_cast<int>(s.dev.dim());
             for (int i = 0; i < v.ndim; ++i) { v.size[i] = s.dev.size(i); v.stride[i] = s.dev.stride(i); }
-            at::Tensor tmp = at::empty(s.dev.sizes(), s.dev.options());
-            DLBB_CALL(dlbb_allreduce(comm_, s.dev.data_ptr(), tmp.data_ptr(), s.dev.numel(), dt,
-                                     to_dlbb_op(opts.reduceOp), algo_, &v, stream()));
-            s.dev.copy_(tmp);
+            // in place on the view: packed by the kernel's first phase, scattered back by its last one
+            DLBB_CALL(dlbb_allreduce_v(comm_, s.dev.data_ptr(), s.dev.data_ptr(), s.dev.numel(), dt,
+                                       to_dlbb_op(opts.reduceOp), algo_, &v, &v, stream()));
         }
         if (opts.reduceOp == c10d::ReduceOp::AVG) s.dev.div_(getSize());
         return finish(c10d::OpType::ALLREDUCE, s, {t});
@@ -219,8 +244,11 @@ class BackendDlbb : public c10d::Backend {
         TORCH_CHECK(tensors.size() == 1, "dlbb backend: one tensor per rank");
         at::Tensor& t = tensors[0];
         const int root = static_cast<int>(opts.rootRank);
-        Staged s = stage_in(t, getRank() == root, /*force_contig=*/true);
-        DLBB_CALL(dlbb_broadcast(comm_, s.dev.data_ptr(), nbytes(s.dev), DLBB_U8, root, stream()));
+        dlbb_view_t v{};
+        const bool view = t.is_cuda() && !t.is_contiguous() && strided_view(t, &v);
+        Staged s = stage_in(t, getRank() == root, /*force_contig=*/!view);
+        if (view) DLBB_CALL(dlbb_broadcast_v(comm_, s.dev.data_ptr(), s.dev.numel(), move_dtype(s.dev.element_size()), root, &v, stream()));
+        else DLBB_CALL(dlbb_broadcast(comm_, s.dev.data_ptr(), nbytes(s.dev), DLBB_U8, root, stream()));
         return finish(c10d::OpType::BROADCAST, s, {t});
     }
 
@@ -229,9 +257,15 @@ class BackendDlbb : public c10d::Backend {
         at::Tensor& t = tensors[0];
         const int root = static_cast<int>(opts.rootRank);
         check_avg(opts.reduceOp, tensors);
-        Staged s = stage_in(t, true, true);
-        DLBB_CALL(dlbb_reduce(comm_, s.dev.data_ptr(), s.dev.data_ptr(), s.dev.numel(),
-                              to_dlbb_dtype(s.dev.scalar_type(), true), to_dlbb_op(opts.reduceOp), root, stream()));
+        dlbb_view_t v{};
+        const bool view = t.is_cuda() && !t.is_contiguous() && strided_view(t, &v);
+        Staged s = stage_in(t, true, /*force_contig=*/!view);
+        if (view)
+            DLBB_CALL(dlbb_reduce_v(comm_, s.dev.data_ptr(), s.dev.data_ptr(), s.dev.numel(), to_dlbb_dtype(s.dev.scalar_type(), true),
+                                    to_dlbb_op(opts.reduceOp), root, &v, &v, stream()));
+        else
+            DLBB_CALL(dlbb_reduce(comm_, s.dev.data_ptr(), s.dev.data_ptr(), s.dev.numel(),
+                                  to_dlbb_dtype(s.dev.scalar_type(), true), to_dlbb_op(opts.reduceOp), root, stream()));
         if (opts.reduceOp == c10d::ReduceOp::AVG && getRank() == root) s.dev.div_(getSize());
         s.copy_back = s.copy_back && getRank() == root;
         return finish(c10d::OpType::REDUCE, s, {t});
@@ -239,9 +273,12 @@ class BackendDlbb : public c10d::Backend {
 
     c10::intrusive_ptr<Work> _allgather_base(at::Tensor& out, at::Tensor& in, const c10d::AllgatherOptions&) override {
         TORCH_CHECK(out.numel() == in.numel() * getSize(), "dlbb backend: all_gather_into_tensor size mismatch");
-        Staged si = stage_in(in, true, true);
+        dlbb_view_t v{};
+        const bool view = in.is_cuda() && !in.is_contiguous() && strided_view(in, &v);
+        Staged si = stage_in(in, true, /*force_contig=*/!view);
         Staged so = stage_in(out, false, true);
-        DLBB_CALL(dlbb_allgather(comm_, si.dev.data_ptr(), so.dev.data_ptr(), nbytes(si.dev), DLBB_U8, nullptr, stream()));
+        if (view) DLBB_CALL(dlbb_allgather(comm_, si.dev.data_ptr(), so.dev.data_ptr(), si.dev.numel(), move_dtype(si.dev.element_size()), &v, stream()));
+        else DLBB_CALL(dlbb_allgather(comm_, si.dev.data_ptr(), so.dev.data_ptr(), nbytes(si.dev), DLBB_U8, nullptr, stream()));
         return finish(c10d::OpType::_ALLGATHER_BASE, so, {out});
     }
 
@@ -250,9 +287,12 @@ class BackendDlbb : public c10d::Backend {
         TORCH_CHECK(ins.size() == 1 && outs.size() == 1 && (int)outs[0].size() == getSize(),
                     "dlbb backend: all_gather expects one input and world_size outputs");
         at::Tensor& in = ins[0];
-        Staged si = stage_in(in, true, true);
+        dlbb_view_t v{};
+        const bool view = in.is_cuda() && !in.is_contiguous() && strided_view(in, &v);
+        Staged si = stage_in(in, true, /*force_contig=*/!view);
         at::Tensor flat = at::empty({getSize(), in.numel()}, si.dev.options());
-        DLBB_CALL(dlbb_allgather(comm_, si.dev.data_ptr(), flat.data_ptr(), nbytes(si.dev), DLBB_U8, nullptr, stream()));
+        if (view) DLBB_CALL(dlbb_allgather(comm_, si.dev.data_ptr(), flat.data_ptr(), si.dev.numel(), move_dtype(si.dev.element_size()), &v, stream()));
+        else DLBB_CALL(dlbb_allgather(comm_, si.dev.data_ptr(), flat.data_ptr(), nbytes(si.dev), DLBB_U8, nullptr, stream()));
         for (int p = 0; p < getSize(); ++p) outs[0][p].copy_(flat[p].view_as(in), /*non_blocking=*/false);
         return done(c10d::OpType::ALLGATHER, outs[0], in.is_cuda());
     }
@@ -262,14 +302,20 @@ class BackendDlbb : public c10d::Backend {
         TORCH_CHECK(ins.size() == 1, "dlbb backend: gather expects one input");
         const int root = static_cast<int>(opts.rootRank);
         at::Tensor& in = ins[0];
-        Staged si = stage_in(in, true, true);
+        dlbb_view_t v{};
+        const bool view = in.is_cuda() && !in.is_contiguous() && strided_view(in, &v);
+        Staged si = stage_in(in, true, /*force_contig=*/!view);
         at::Tensor flat;
         if (getRank() == root) {
             TORCH_CHECK(outs.size() == 1 && (int)outs[0].size() == getSize(), "dlbb backend: gather needs world_size outputs on the root");
             flat = at::empty({getSize(), in.numel()}, si.dev.options());
         }
-        DLBB_CALL(dlbb_gather(comm_, si.dev.data_ptr(), flat.defined() ? flat.data_ptr() : nullptr, nbytes(si.dev), DLBB_U8,
-                              root, stream()));
+        if (view)
+            DLBB_CALL(dlbb_gather_v(comm_, si.dev.data_ptr(), flat.defined() ? flat.data_ptr() : nullptr, si.dev.numel(),
+                                    move_dtype(si.dev.element_size()), root, &v, stream()));
+        else
+            DLBB_CALL(dlbb_gather(comm_, si.dev.data_ptr(), flat.defined() ? flat.data_ptr() : nullptr, nbytes(si.dev), DLBB_U8,
+                                  root, stream()));
         std::vector<at::Tensor> res;
         if (getRank() == root) {
             for (int p = 0; p < getSize(); ++p) outs[0][p].copy_(flat[p].view_as(in));

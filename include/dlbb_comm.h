@@ -96,6 +96,18 @@ int dlbb_allreduce_multi(dlbb_comm_t* c, void* const* bufs, const int64_t* count
  * residual add (K16 without the GEMM; ref models.py:95 + :173/:188). */
 int dlbb_allreduce_residual_bf16(dlbb_comm_t* c, const void* in, const void* residual, void* out,
                                  int64_t count, void* stream);
+/* Strided tensors (K12): *_v variants take view descriptors for the source and / or the destination; the kernels
+ * gather the source view while packing and scatter into the destination view while unpacking - there is no
+ * .contiguous() copy before or after (no counterpart in the reference, whose tensors are dense: SURVEY.md N4).
+ * For broadcast the same view describes the tensor on every rank. */
+int dlbb_allreduce_v(dlbb_comm_t* c, const void* in, void* out, int64_t count, int dtype, int op, int algo,
+                     const dlbb_view_t* in_view, const dlbb_view_t* out_view, void* stream);
+int dlbb_broadcast_v(dlbb_comm_t* c, void* buf, int64_t count, int dtype, int root, const dlbb_view_t* buf_view,
+                     void* stream);
+int dlbb_reduce_v(dlbb_comm_t* c, const void* in, void* out, int64_t count, int dtype, int op, int root,
+                  const dlbb_view_t* in_view, const dlbb_view_t* out_view, void* stream);
+int dlbb_gather_v(dlbb_comm_t* c, const void* in, void* out, int64_t count, int dtype, int root,
+                  const dlbb_view_t* in_view, void* stream);
 int dlbb_reduce_scatter(dlbb_comm_t* c, const void* in, void* out, int64_t count_per_rank,
                         int dtype, int op, void* stream);
 int dlbb_allgather(dlbb_comm_t* c, const void* in, void* out, int64_t count_per_rank, int dtype,

@@ -147,6 +147,88 @@ dist.destroy_process_group()
     assert r.returncode == 0 and r.stdout.count("NATIVE_OK") == n, r.stdout[-3000:] + r.stderr[-3000:]
 
 
+def test_strided_views_are_packed_and_unpacked_in_kernel(native_lib, tmp_path):
+    """K12: non-contiguous tensors through all-reduce / broadcast / reduce / all-gather / gather of the process group -
+    3-D [b, s, h] slices of a wider tensor (vector path) and a transposed fp32 matrix (element path); the bytes of the
+    base tensor outside the view must stay untouched."""
+    script = tmp_path / "v.py"
+    script.write_text(f"""
+import sys; sys.path[:0] = [{str(ROOT)!r}, {str(ROOT / 'compat')!r}]
+import torch, torch.distributed as dist, oneccl_bindings_for_pytorch
+dist.init_process_group('ccl')
+r, w = dist.get_rank(), dist.get_world_size()
+dev = 'cuda'
+def mk(rank, kind):
+    g = torch.Generator().manual_seed(100 + rank)
+    if kind == '3d':
+        base = torch.randn(3, 40, 256, generator=g).bfloat16().to(dev); return base, base[:, :, :128]
+    if kind == 'big':
+        base = torch.randn(8, 512, 2048, generator=g).bfloat16().to(dev); return base, base[:, :, 1024:]
+    base = torch.randn(37, 53, generator=g).to(dev); return base, base.t()
+for kind in ('3d', 'big', 't'):
+    views = [mk(q, kind)[1] for q in range(w)]
+    tot = sum(v.double() for v in views)
+    tol = 2e-2 if kind != 't' else 1e-5
+    def fresh():
+        base, v = mk(r, kind); return base, v, base.clone()
+    def outside_untouched(base, v, before):
+        b2, bb = base.clone(), before.clone()
+        (b2[:, :, :128] if kind == '3d' else b2[:, :, 1024:] if kind == 'big' else b2.t()).zero_()
+        (bb[:, :, :128] if kind == '3d' else bb[:, :, 1024:] if kind == 'big' else bb.t()).zero_()
+        return torch.equal(b2, bb)
+    base, v, before = fresh(); assert not v.is_contiguous()
+    dist.all_reduce(v)
+    assert ((v.double() - tot).abs().max() / tot.abs().max()).item() < tol, ('allreduce', kind)
+    assert outside_untouched(base, v, before), ('allreduce outside', kind)
+    base, v, before = fresh(); dist.broadcast(v, src=w - 1)
+    assert torch.equal(v, views[w - 1]), ('broadcast', kind)
+    assert outside_untouched(base, v, before), ('broadcast outside', kind)
+    base, v, before = fresh(); dist.reduce(v, dst=0)
+    if r == 0: assert ((v.double() - tot).abs().max() / tot.abs().max()).item() < tol, ('reduce', kind)
+    else: assert torch.equal(v, views[r]), ('reduce left a non-root tensor changed', kind)
+    base, v, before = fresh()
+    outs = [torch.empty(v.shape, dtype=v.dtype, device=dev) for _ in range(w)]; dist.all_gather(outs, v)
+    assert all(torch.equal(o, views[q]) for q, o in enumerate(outs)), ('allgather', kind)
+    outs = [torch.empty(v.shape, dtype=v.dtype, device=dev) for _ in range(w)] if r == 0 else None
+    dist.gather(v, gather_list=outs, dst=0)
+    if r == 0: assert all(torch.equal(o, views[q]) for q, o in enumerate(outs)), ('gather', kind)
+torch.cuda.synchronize(); dist.barrier()
+import sys as _s; _s.stdout.write(f'VIEWS_OK {{r}}\n')
+dist.destroy_process_group()
+""")
+    n = nranks()
+    r = run([BIN / "mpirun", "-np", n, sys.executable, script])
+    assert r.returncode == 0 and r.stdout.count("VIEWS_OK") == n, r.stdout[-3000:] + r.stderr[-3000:]
+
+
+def test_coalesced_allreduce_is_one_launch(native_lib, tmp_path):
+    """K13: all_reduce_coalesced of many small tensors goes through the multi-tensor kernel (one launch per bucket),
+    DLBB_FUSION=0 through one collective per tensor; both give the same sums."""
+    script = tmp_path / "c.py"
+    script.write_text(f"""
+import sys, os; sys.path[:0] = [{str(ROOT)!r}, {str(ROOT / 'compat')!r}]
+import torch, torch.distributed as dist, oneccl_bindings_for_pytorch
+from distributed_llm_backend_benchmark_b200 import _lib
+dist.init_process_group('ccl')
+r, w = dist.get_rank(), dist.get_world_size()
+ts = [torch.full((n,), float(r + 1 + i), device='cuda', dtype=dt) for i, (n, dt) in enumerate(
+      [(5, torch.float32), (1000, torch.bfloat16), (77, torch.float32), (4096, torch.float16), (3, torch.float64)] * 8)]
+want = [sum(q + 1 + i for q in range(w)) for i in range(len(ts))]
+torch.cuda.synchronize(); n0 = _lib.launch_count()
+dist.all_reduce_coalesced(ts)
+torch.cuda.synchronize(); launches = _lib.launch_count() - n0
+for t, x in zip(ts, want): assert (t.double() == x).all(), (t.dtype, t[0].item(), x)
+fused = os.environ.get('DLBB_FUSION', '1') == '1'
+assert (launches <= 4) if (fused and w > 1) else (launches >= len(ts) or w == 1), launches
+sys.stdout.write(f'COALESCED_OK {{r}} {{launches}}\n')
+dist.destroy_process_group()
+""")
+    n = nranks()
+    for fusion in ("1", "0"):
+        r = run([BIN / "mpirun", "-np", n, sys.executable, script], env={"DLBB_FUSION": fusion})
+        assert r.returncode == 0 and r.stdout.count("COALESCED_OK") == n, r.stdout[-3000:] + r.stderr[-3000:]
+
+
 def test_run_mpi_on_gpu(native_lib, tmp_path):
     n = nranks()
     cfg = tmp_path / "small.yaml"
