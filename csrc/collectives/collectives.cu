@@ -1055,7 +1055,7 @@ static ViewDev make_view(const dlbb_view_t* v) {
 
 // The strided destination of the running *_v call (comm_internal.h: out_view / out_base), for the kernels' unpack side.
 static ViewDev out_view_of(const dlbb_comm* c) {
-    ViewDev v = out_view_of(c);
+    ViewDev v = make_view(c->out_view);
     v.base = c->out_view ? c->out_base : 0;
     return v;
 }
