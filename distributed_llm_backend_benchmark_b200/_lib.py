@@ -34,6 +34,8 @@ _SIGNATURES = {
     "dlbb_layernorm_bwd_scratch_bytes": (c_size_t, [c_int, c_int]),
     "dlbb_layernorm_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                                    c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p]),
+    "dlbb_layernorm_bwd_ex": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                                      c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p]),
     "dlbb_gelu_fwd": (c_int, [c_void_p, c_void_p, c_int64, c_void_p]),
     "dlbb_gelu_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_void_p]),
     "dlbb_add": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_void_p]),

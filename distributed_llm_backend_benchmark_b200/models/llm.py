@@ -113,6 +113,10 @@ class LLMEngine:
         self.eps = eps
         self.training = training
         self.dense_qkv_backward = os.environ.get("DLBB_DENSE_QKV_BWD", "0") == "1"
+        # Gradient buckets handed to the data-parallel engine: "matrix" = one per weight matrix, announced right after
+        # that matrix's wgrad GEMM has been enqueued (the exchange of dW_down starts while dW_up is still being computed);
+        # "layer" = one per layer.  None = let the data-parallel engine choose (matrix when it overlaps, else layer).
+        self.bucket_mode = os.environ.get("DLBB_DP_BUCKETS")
         H, F, L = cfg.hidden_size, cfg.ffn_intermediate, cfg.num_layers
         self.layer_numel = cfg.params_per_layer(tp_size)
         self.total_numel = L * self.layer_numel + 2 * H
@@ -170,11 +174,19 @@ class LLMEngine:
         self.lnf_b.zero_()
 
     def bucket_slices(self) -> list[tuple[int, int]]:
-        """(offset, numel) of each gradient bucket in backward-completion order: the final
-        LayerNorm first, then layers L-1 .. 0."""
-        L = self.cfg.num_layers
-        out = [(L * self.layer_numel, 2 * self.cfg.hidden_size)]
-        out += [(i * self.layer_numel, self.layer_numel) for i in reversed(range(L))]
+        """(offset, numel) of each gradient bucket in backward-completion order: the final LayerNorm first, then
+        layers L-1 .. 0 - as one bucket per layer, or (bucket_mode "matrix") as W_down, W_up, W_o, W_qkv and the
+        layer's four LayerNorm vectors, each in the order in which backward completes them."""
+        L, H, F = self.cfg.num_layers, self.cfg.hidden_size, self.cfg.ffn_intermediate
+        out = [(L * self.layer_numel, 2 * H)]
+        for i in reversed(range(L)):
+            base = i * self.layer_numel
+            if self.bucket_mode == "matrix":
+                n_qkv, n_o, n_up, n_down = H * 3 * H, H * H, H * F, F * H
+                o_qkv, o_o, o_up, o_down = base, base + n_qkv, base + n_qkv + n_o, base + n_qkv + n_o + n_up
+                out += [(o_down, n_down), (o_up, n_up), (o_o, n_o), (o_qkv, n_qkv), (o_down + n_down, 4 * H)]
+            else:
+                out.append((base, self.layer_numel))
         return out
 
     def get_num_parameters(self) -> int:
@@ -291,42 +303,53 @@ class LLMEngine:
         # ---------------- loss and its gradient
         ops.mse_loss(a["y"], target.reshape(tokens, H), grad_scale=grad_scale, loss_out=a["loss"], dy=a["dy"])
         # ---------------- backward
-        dx, dgf, dbf = ops.layernorm_bwd(a["dy"], xs[L], mf, rf, self.lnf_g, None, dx=a["dxa"])
-        self.glnf_g.copy_(dgf)
-        self.glnf_b.copy_(dbf)
-        if on_bucket_ready:
-            on_bucket_ready(0)
+        dx, _, _ = ops.layernorm_bwd(a["dy"], xs[L], mf, rf, self.lnf_g, None, dx=a["dxa"], dgamma_out=self.glnf_g,
+                                     dbeta_out=self.glnf_b)   # parameter gradients land in the bucket as bf16
+        fine = self.bucket_mode == "matrix"
+        ready = 0   # index into bucket_slices() of the next bucket to announce
+
+        def announce(only_if_fine: bool = False):
+            nonlocal ready
+            if only_if_fine and not fine:
+                return
+            if on_bucket_ready:
+                on_bucket_ready(ready)
+            ready += 1
+
+        announce()
         spare = a["dxb"]
         for n, i in enumerate(reversed(range(L))):
             lv, gv = self.layers[i], self.glayers[i]
             # FFN
             ops.matmul(a["a"][i], dx, transpose_a=True, out=gv.wdown)                       # dW_down = a^T dx3
+            announce(True)
             ops.matmul(dx, lv.wdown, transpose_b=True, epilogue="mul_dgelu", aux=a["z"][i], out=a["dz"])
             ops.matmul(a["h2"][i], a["dz"], transpose_a=True, out=gv.wup)                    # dW_up = h2^T dz
+            announce(True)
             ops.matmul(a["dz"], lv.wup, transpose_b=True, out=a["dh"])                       # dh2
             m2, r2 = a["st2"][i]
-            dx2, dg, db = ops.layernorm_bwd(a["dh"], a["x2"][i], m2, r2, lv.ln2_g, dx, dx=spare)
-            gv.ln2_g.copy_(dg)
-            gv.ln2_b.copy_(db)
+            dx2, _, _ = ops.layernorm_bwd(a["dh"], a["x2"][i], m2, r2, lv.ln2_g, dx, dx=spare, dgamma_out=gv.ln2_g,
+                                          dbeta_out=gv.ln2_b)
             # "attention" + projections
             attn = a["qkv"][i][:, :H]
             ops.matmul(attn, dx2, transpose_a=True, out=gv.wo)                               # dW_o
+            announce(True)
             ops.matmul(dx2, lv.wo, transpose_b=True, out=a["dattn"])                         # d attn
             if self.dense_qkv_backward:
                 # what autograd would run: zero-padded d(qkv) through the full 3H-wide GEMMs
                 a["dqkv"][:, :H].copy_(a["dattn"])
                 ops.matmul(a["h1"][i], a["dqkv"], transpose_a=True, out=gv.wqkv)
+                announce(True)
                 ops.matmul(a["dqkv"], lv.wqkv, transpose_b=True, out=a["dh"])
             else:
                 # d(qkv) is structurally zero outside the first H columns, so only that block of
                 # dW_qkv is non-zero (the rest of the bucket stays at its initial zeros).
                 ops.matmul(a["h1"][i], a["dattn"], transpose_a=True, out=gv.wqkv[:, :H])
+                announce(True)
                 ops.matmul(a["dattn"], lv.wqkv[:, :H], transpose_b=True, out=a["dh"])
             m1, r1 = a["st1"][i]
-            dx1, dg, db = ops.layernorm_bwd(a["dh"], xs[i], m1, r1, lv.ln1_g, dx2, dx=dx)
-            gv.ln1_g.copy_(dg)
-            gv.ln1_b.copy_(db)
+            dx1, _, _ = ops.layernorm_bwd(a["dh"], xs[i], m1, r1, lv.ln1_g, dx2, dx=dx, dgamma_out=gv.ln1_g,
+                                          dbeta_out=gv.ln1_b)
             dx, spare = dx1, dx2
-            if on_bucket_ready:
-                on_bucket_ready(n + 1)
+            announce()   # the layer bucket, or (matrix mode) the layer's LayerNorm vectors
         return a["loss"]

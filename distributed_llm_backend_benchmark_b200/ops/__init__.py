@@ -147,8 +147,12 @@ def _scratch(device: torch.device, nbytes: int, key: str) -> torch.Tensor:
 
 def layernorm_bwd(dy: torch.Tensor, x: torch.Tensor, mean: torch.Tensor, rstd: torch.Tensor,
                   gamma: torch.Tensor, dres: torch.Tensor | None = None, want_param_grads: bool = True,
-                  dx: torch.Tensor | None = None):
-    """Returns (dx, dgamma, dbeta); dx already includes ``dres`` (the residual-branch gradient)."""
+                  dx: torch.Tensor | None = None, dgamma_out: torch.Tensor | None = None,
+                  dbeta_out: torch.Tensor | None = None):
+    """Returns (dx, dgamma, dbeta); dx already includes ``dres`` (the residual-branch gradient).
+
+    ``dgamma_out`` / ``dbeta_out`` (bf16 [cols], e.g. slices of a flat gradient bucket) receive the parameter
+    gradients directly from the kernel that folds the partial sums; they are then what is returned."""
     cols = x.shape[-1]
     rows = x.numel() // cols
     if dx is None:
@@ -163,12 +167,24 @@ def layernorm_bwd(dy: torch.Tensor, x: torch.Tensor, mean: torch.Tensor, rstd: t
         if dres is not None:
             r = r + dres.float().reshape(rows, cols)
         dx.copy_(r.reshape(x.shape).to(dx.dtype))
+        if dgamma_out is not None:
+            dgamma_out.copy_((dyf * xh).sum(0).to(dgamma_out.dtype))
+            dbeta_out.copy_(dyf.sum(0).to(dbeta_out.dtype))
+            return dx, dgamma_out, dbeta_out
         if want_param_grads:
             return dx, (dyf * xh).sum(0), dyf.sum(0)
         return dx, None, None
     lib = _lib.load()
     nbytes = lib.dlbb_layernorm_bwd_scratch_bytes(rows, cols)
     scratch = _scratch(x.device, nbytes, "ln_bwd")
+    if dgamma_out is not None:
+        assert dbeta_out is not None and dgamma_out.dtype == torch.bfloat16 and dbeta_out.dtype == torch.bfloat16
+        assert dgamma_out.is_contiguous() and dbeta_out.is_contiguous() and dgamma_out.numel() == cols
+        rc = lib.dlbb_layernorm_bwd_ex(dy.data_ptr(), x.data_ptr(), mean.data_ptr(), rstd.data_ptr(), gamma.data_ptr(),
+                                       _ptr(dres), dx.data_ptr(), None, None, dgamma_out.data_ptr(), dbeta_out.data_ptr(),
+                                       scratch.data_ptr(), rows, cols, _stream(x))
+        _lib.check(rc, "layernorm_bwd")
+        return dx, dgamma_out, dbeta_out
     dgamma = torch.empty(cols, dtype=torch.float32, device=x.device) if want_param_grads else None
     dbeta = torch.empty(cols, dtype=torch.float32, device=x.device) if want_param_grads else None
     rc = lib.dlbb_layernorm_bwd(dy.data_ptr(), x.data_ptr(), mean.data_ptr(), rstd.data_ptr(), gamma.data_ptr(),

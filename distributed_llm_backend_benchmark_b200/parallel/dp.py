@@ -40,6 +40,10 @@ class DataParallelTrainer:
         self.overlap = overlap and self.cuda and _os.environ.get("DLBB_DP_OVERLAP", default_overlap) == "1"
         self._overlap_ctas = int(_os.environ.get("DLBB_ADAM_OVERLAP_CTAS", "148"))
         self.skip_optimizer = _os.environ.get("DLBB_DEBUG_SKIP_OPT", "0") == "1"   # debugging aid, invalidates results
+        if engine.bucket_mode is None:
+            # one bucket per weight matrix when the exchange overlaps backward (it then starts a GEMM earlier and the
+            # exposed tail after the last layer is a quarter of a layer), one per layer when the optimizer runs afterwards
+            engine.bucket_mode = "matrix" if self.overlap else "layer"
         self.buckets = engine.bucket_slices()
         # Optimizer state is sharded: rank r owns elements [r*shard, (r+1)*shard) of every bucket
         # (buckets are padded up to a multiple of world*8 elements on the comm side).

@@ -72,6 +72,11 @@ size_t dlbb_layernorm_bwd_scratch_bytes(int rows, int cols);
 int dlbb_layernorm_bwd(const void* dy, const void* x, const float* mean, const float* rstd,
                        const void* gamma, const void* dres, void* dx, float* dgamma, float* dbeta,
                        void* scratch, int rows, int cols, void* stream);
+/* Same, with optional bf16 copies of the parameter gradients (dgamma_bf16 / dbeta_bf16, [cols]) written by the fold
+ * kernel itself - the training engine points them into its flat gradient bucket, so no cast-and-copy follows. */
+int dlbb_layernorm_bwd_ex(const void* dy, const void* x, const float* mean, const float* rstd,
+                          const void* gamma, const void* dres, void* dx, float* dgamma, float* dbeta,
+                          void* dgamma_bf16, void* dbeta_bf16, void* scratch, int rows, int cols, void* stream);
 
 /* LayerNorm backward that allocates nothing and needs no caller scratch.  It has no counterpart
  * in the reference; it exists for callers that may not call cudaMalloc where they need the op (a
