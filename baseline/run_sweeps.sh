@@ -15,6 +15,6 @@ for arm in dlbb nccl; do
       DLBB_SWEEP_MAX_MB=${MAX_MB_3D:-600} DLBB_OUTPUT_DIR="$OUT/3d_$arm" timeout 600 deepspeed --num_gpus $NP --master_port 29702 dsccl.py > "$OUT/3d_$arm.log" 2>&1; echo "3d $arm rc=$?" )
 done
 unset DLBB_SWEEP_BACKEND
-( cd "$ROOT/collectives/3d" && DLBB_SWEEP_STRIDED=1 DLBB_SWEEP_BATCH=8 DLBB_SWEEP_SEQ=1,2048 DLBB_SWEEP_HIDDEN=4096 DLBB_SWEEP_OPS=allreduce,allgather \
+( cd "$ROOT/collectives/3d" && DLBB_SWEEP_STRIDED=1 DLBB_SWEEP_BATCH=${BATCH_STRIDED:-1,8} DLBB_SWEEP_SEQ=${SEQ_STRIDED:-1,2048} DLBB_SWEEP_HIDDEN=4096 DLBB_SWEEP_OPS=${OPS_3D:-allreduce,allgather,broadcast,reduce,gather} \
     DLBB_OUTPUT_DIR="$OUT/3d_dlbb_strided" timeout 300 deepspeed --num_gpus $NP --master_port 29703 dsccl.py > "$OUT/3d_strided.log" 2>&1; echo "3d strided rc=$?" )
 python "$ROOT/baseline/compare.py" "$OUT" | tee "$OUT/compare.md"
