@@ -274,10 +274,18 @@ def main() -> None:
     # ---------------- second half of BASELINE.json's metric: collective bus bandwidth, ours next to NCCL
     collectives = None
     if world > 1 and comm is not None and not args.no_collectives:
+        # NCCL prints its version banner on stdout when it initialises: keep stdout for the one JSON line
+        sys.stdout.flush()
+        saved_stdout = os.dup(1)
+        os.dup2(2, 1)
         try:
             collectives = collective_table(comm, dev, rank, world, barrier, max_over_ranks)
         except Exception as e:  # noqa: BLE001 - the headline number must survive a failure here
             collectives = {"error": repr(e)}
+        finally:
+            sys.stdout.flush()
+            os.dup2(saved_stdout, 1)
+            os.close(saved_stdout)
 
     if rank == 0:
         mc = LLMConfig.from_dict(cfg)

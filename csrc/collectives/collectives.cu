@@ -1236,7 +1236,11 @@ static int try_zero_copy(dlbb_comm* c, const void* buf, int64_t bytes, int64_t g
                          const void* raw = nullptr) {
     *ok = false;
     if (c->world == 1 || c->zero_copy_min == 0) return 0;
-    if (gate_bytes < (int64_t)c->zero_copy_min && symm_segment_of(c, raw ? raw : buf, static_cast<size_t>(bytes)) < 0) return 0;
+    // (below 256 KiB the staged single-barrier kernels are as fast or faster than the two-barrier direct ones)
+    static const int64_t symm_min = getenv("DLBB_SYMM_MIN_BYTES") ? atoll(getenv("DLBB_SYMM_MIN_BYTES")) : (256 << 10);
+    if (gate_bytes < (int64_t)c->zero_copy_min &&
+        (gate_bytes < symm_min || symm_segment_of(c, raw ? raw : buf, static_cast<size_t>(bytes)) < 0))
+        return 0;
     return peer_registry_resolve(c, c->reg, buf, static_cast<size_t>(bytes), pv, ok);
 }
 
@@ -1680,7 +1684,9 @@ int dlbb_reduce_scatter(dlbb_comm_t* c, const void* in, void* out, int64_t cpr, 
             const bool nvls_ok = dlbb_comm_has_multicast(c) && op == DLBB_SUM &&
                                  (dtype == DLBB_F16 || dtype == DLBB_BF16 || dtype == DLBB_F32);
             DirectPlan pl{};
-            pl.mc_src = pv.mc && nvls_ok && env_flag("DLBB_MC_REDUCE_SCATTER", true);
+            // (measured: the switch reduction never beats the peer loads here - 334 vs 648 GB/s on 2 GPUs, 520 vs 656 on 4,
+            //  626 vs 634 on 8 - so multimem.ld_reduce is opt-in for reduce-scatter)
+            pl.mc_src = pv.mc && nvls_ok && env_flag("DLBB_MC_REDUCE_SCATTER", false);
             pl.sink = SINK_ONE;
             pl.a.in = pv;
             pl.a.out.ptr[0] = static_cast<char*>(out);
@@ -2020,6 +2026,63 @@ int dlbb_allreduce_multi(dlbb_comm_t* c, void* const* bufs, const int64_t* count
         used += slot;
     }
     return flush();
+}
+
+// All-to-all on lists of tensors (the torch / mpi4py list API the sweeps use, collectives/1d/dsccl.py:134-146): chunk p of
+// the message is its own tensor on both sides.  The pieces carry each tensor's offset from the first one, so the kernel
+// packs straight out of the list and pulls straight into it - no flattening copy before or after.
+int dlbb_alltoall_ptrs(dlbb_comm_t* c, const void* const* in_ptrs, void* const* out_ptrs, int64_t bytes_per_peer, void* stream) {
+    const int64_t total = bytes_per_peer;
+    const int64_t cap = static_cast<int64_t>(c->stage_bytes) / c->world / 64 * 64;
+    DLBB_REQUIRE(cap > 0, "alltoall: staging too small");
+    const char* in0 = static_cast<const char*>(in_ptrs[0]);
+    char* out0 = static_cast<char*>(out_ptrs[0]);
+    for (int64_t done = 0; done < total || (total == 0 && done == 0); done += cap) {
+        const int64_t n = std::min(cap, total - done);
+        if (n <= 0) break;
+        const int64_t slot = (n + 63) / 64 * 64;
+        PieceList pack{}, pull{};
+        pack.count = c->world;
+        for (int p = 0; p < c->world; ++p)
+            pack.p[p] = Piece{0, (static_cast<const char*>(in_ptrs[p]) - in0) + done, p * slot, n};
+        pull.count = c->world;
+        for (int i = 0; i < c->world; ++i) {
+            const int p = (c->rank + i) % c->world;
+            pull.p[i] = Piece{p, c->rank * slot, (static_cast<char*>(out_ptrs[p]) - out0) + done, n};
+        }
+        const int rc = launch_move(c, in0, out0, pack, pull, ViewDev{}, 1, n * c->world, static_cast<cudaStream_t>(stream));
+        if (rc) return rc;
+    }
+    return 0;
+}
+
+// All-gather / gather into a LIST of output tensors (torch's list API, collectives/1d/dsccl.py:76,102): rank p's
+// contribution is pulled straight into out_ptrs[p].  root < 0: all-gather; otherwise only the root receives.
+int dlbb_allgather_ptrs(dlbb_comm_t* c, const void* in, void* const* out_ptrs, int64_t count, int dtype, int root,
+                        const dlbb_view_t* in_view, void* stream) {
+    const int64_t es = (int64_t)dtype_size(dtype);
+    DLBB_REQUIRE(es != 0, "allgather: unsupported dtype %d", dtype);
+    DLBB_REQUIRE(root < c->world, "gather: bad root %d", root);
+    const int64_t total = count * es, cap = static_cast<int64_t>(c->stage_bytes) / 64 * 64;
+    const ViewDev view = make_view(in_view);
+    const bool receiver = root < 0 || c->rank == root;
+    char* out0 = receiver ? static_cast<char*>(out_ptrs[0]) : nullptr;
+    for (int64_t done = 0; done < total; done += cap) {
+        const int64_t n = std::min(cap, total - done);
+        PieceList pack{}, pull{};
+        pack.count = 1;
+        pack.p[0] = Piece{0, done, 0, n};
+        if (receiver) {
+            pull.count = c->world;
+            for (int i = 0; i < c->world; ++i) {
+                const int p = (c->rank + i) % c->world;
+                pull.p[i] = Piece{p, 0, (static_cast<char*>(out_ptrs[p]) - out0) + done, n};
+            }
+        }
+        const int rc = launch_move(c, in, out0, pack, pull, view, (int)es, n * c->world, static_cast<cudaStream_t>(stream));
+        if (rc) return rc;
+    }
+    return 0;
 }
 
 }  // extern "C"

@@ -381,7 +381,10 @@ static int launch_reduce_pull(dlbb_comm* c, int dtype, int op, const PeerView& p
 
 static int launch_bcast_relay(dlbb_comm* c, const PeerView& pv, int64_t nvec, int root, cudaStream_t s) {
     const int P = c->world;
-    const bool mc = pv.mc != nullptr && env_flag("DLBB_BCAST_MC", true);
+    // multimem relay for messages below 8 MiB (no flags, one hop less: 158 vs 101 GB/s at 4 MiB on 8 GPUs), the flag-
+    // driven peer relay above (multicast delivery tops out near 400-420 GB/s per GPU, the peer pulls reach 540-600)
+    static const int64_t mc_max = getenv("DLBB_BCAST_MC_MAX_BYTES") ? atoll(getenv("DLBB_BCAST_MC_MAX_BYTES")) : (8ll << 20);
+    const bool mc = pv.mc != nullptr && env_flag("DLBB_BCAST_MC", true) && (nvec << 4) < mc_max;
     // P2P: every CTA walks its row chunk by chunk (wait -> load -> store -> signal, ~3 NVLink round trips per chunk), so
     // the pipeline is fed by the number of rows: two CTAs per SM unless DLBB_CTAS says otherwise.
     static const int kRelayChunkVecs = getenv("DLBB_RELAY_CHUNK_KB") ? std::max(1, atoi(getenv("DLBB_RELAY_CHUNK_KB"))) * 64

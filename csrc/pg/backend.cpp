@@ -290,6 +290,21 @@ class BackendDlbb : public c10d::Backend {
         dlbb_view_t v{};
         const bool view = in.is_cuda() && !in.is_contiguous() && strided_view(in, &v);
         Staged si = stage_in(in, true, /*force_contig=*/!view);
+        if (in.is_cuda() && move_dtype(in.element_size()) >= 0) {
+            // device list: every rank's contribution is pulled straight into its output tensor (dense temporaries stand in
+            // for outputs that are not dense, so that every rank runs the same kernel)
+            const bool direct = list_is_dense_cuda(outs[0], in);
+            std::vector<void*> op(getSize());
+            std::vector<at::Tensor> tmp;
+            for (int p = 0; p < getSize(); ++p) {
+                if (!direct) tmp.push_back(at::empty(in.sizes(), in.options().memory_format(at::MemoryFormat::Contiguous)));
+                op[p] = direct ? outs[0][p].data_ptr() : tmp[p].data_ptr();
+            }
+            DLBB_CALL(dlbb_allgather_ptrs(comm_, si.dev.data_ptr(), op.data(), si.dev.numel(), move_dtype(si.dev.element_size()), -1,
+                                          view ? &v : nullptr, stream()));
+            for (size_t p = 0; p < tmp.size(); ++p) outs[0][p].copy_(tmp[p].view_as(outs[0][p]));
+            return done(c10d::OpType::ALLGATHER, outs[0], true);
+        }
         at::Tensor flat = at::empty({getSize(), in.numel()}, si.dev.options());
         if (view) DLBB_CALL(dlbb_allgather(comm_, si.dev.data_ptr(), flat.data_ptr(), si.dev.numel(), move_dtype(si.dev.element_size()), &v, stream()));
         else DLBB_CALL(dlbb_allgather(comm_, si.dev.data_ptr(), flat.data_ptr(), nbytes(si.dev), DLBB_U8, nullptr, stream()));
@@ -306,10 +321,26 @@ class BackendDlbb : public c10d::Backend {
         const bool view = in.is_cuda() && !in.is_contiguous() && strided_view(in, &v);
         Staged si = stage_in(in, true, /*force_contig=*/!view);
         at::Tensor flat;
-        if (getRank() == root) {
+        if (getRank() == root)
             TORCH_CHECK(outs.size() == 1 && (int)outs[0].size() == getSize(), "dlbb backend: gather needs world_size outputs on the root");
-            flat = at::empty({getSize(), in.numel()}, si.dev.options());
+        if (in.is_cuda() && move_dtype(in.element_size()) >= 0) {
+            // CUDA tensors (on every rank: the SPMD contract): the kernel writes the root's list directly; a list that is
+            // not dense is gathered into dense temporaries first - the choice of kernel must not depend on the rank
+            std::vector<void*> op(getSize(), nullptr);
+            std::vector<at::Tensor> tmp;
+            if (getRank() == root) {
+                const bool direct = list_is_dense_cuda(outs[0], in);
+                for (int p = 0; p < getSize(); ++p) {
+                    if (!direct) tmp.push_back(at::empty(in.sizes(), in.options().memory_format(at::MemoryFormat::Contiguous)));
+                    op[p] = direct ? outs[0][p].data_ptr() : tmp[p].data_ptr();
+                }
+            }
+            DLBB_CALL(dlbb_allgather_ptrs(comm_, si.dev.data_ptr(), op.data(), si.dev.numel(), move_dtype(si.dev.element_size()), root,
+                                          view ? &v : nullptr, stream()));
+            for (size_t p = 0; p < tmp.size(); ++p) outs[0][p].copy_(tmp[p].view_as(outs[0][p]));
+            return done(c10d::OpType::GATHER, getRank() == root ? outs[0] : std::vector<at::Tensor>{}, true);
         }
+        if (getRank() == root) flat = at::empty({getSize(), in.numel()}, si.dev.options());
         if (view)
             DLBB_CALL(dlbb_gather_v(comm_, si.dev.data_ptr(), flat.defined() ? flat.data_ptr() : nullptr, si.dev.numel(),
                                     move_dtype(si.dev.element_size()), root, &v, stream()));
@@ -384,6 +415,17 @@ class BackendDlbb : public c10d::Backend {
         for (int p = 0; p < getSize(); ++p)
             TORCH_CHECK(ins[p].numel() == n && outs[p].numel() == n, "dlbb backend: all_to_all supports equal chunk sizes only");
         const bool cuda = ins[0].is_cuda();
+        bool dense = cuda;
+        for (int p = 0; p < getSize() && dense; ++p)
+            dense = ins[p].is_cuda() && outs[p].is_cuda() && ins[p].is_contiguous() && outs[p].is_contiguous();
+        if (dense) {   // device lists: the kernel reads and writes the list's tensors directly
+            c10::cuda::CUDAGuard g(dev_);
+            std::vector<const void*> ip(getSize());
+            std::vector<void*> op(getSize());
+            for (int p = 0; p < getSize(); ++p) { ip[p] = ins[p].data_ptr(); op[p] = outs[p].data_ptr(); }
+            DLBB_CALL(dlbb_alltoall_ptrs(comm_, ip.data(), op.data(), n * ins[0].element_size(), stream()));
+            return done(c10d::OpType::ALLTOALL, outs, true);
+        }
         auto options = ins[0].options().device(c10::Device(c10::kCUDA, dev_));
         at::Tensor fin = at::empty({getSize(), n}, options), fout = at::empty({getSize(), n}, options);
         for (int p = 0; p < getSize(); ++p) fin[p].copy_(ins[p].reshape({-1}));
@@ -411,6 +453,16 @@ class BackendDlbb : public c10d::Backend {
     }
 
   private:
+    // every tensor of an output list is a dense CUDA tensor of the input's size on this device
+    bool list_is_dense_cuda(const std::vector<at::Tensor>& list, const at::Tensor& like) const {
+        if (!like.is_cuda()) return false;
+        for (const auto& t : list)
+            if (!t.is_cuda() || t.get_device() != dev_ || !t.is_contiguous() || t.numel() != like.numel() ||
+                t.element_size() != like.element_size())
+                return false;
+        return true;
+    }
+
     // ReduceOp::AVG is SUM followed by a division: only meaningful on floating-point tensors
     static void check_avg(const c10d::ReduceOp& op, const std::vector<at::Tensor>& ts) {
         if (op != c10d::ReduceOp::AVG) return;

@@ -123,6 +123,14 @@ int dlbb_scatter(dlbb_comm_t* c, const void* in, void* out, int64_t count, int d
 /* all-to-all: chunk p of `in` goes to rank p; chunk r of `out` comes from rank r. */
 int dlbb_alltoall(dlbb_comm_t* c, const void* in, void* out, int64_t count_per_rank, int dtype,
                   void* stream);
+/* All-gather (root < 0) or gather (to `root`) into a list of output tensors: rank p's `count` elements land in
+ * out_ptrs[p]; the input may be a strided view.  out_ptrs is only read on ranks that receive. */
+int dlbb_allgather_ptrs(dlbb_comm_t* c, const void* in, void* const* out_ptrs, int64_t count, int dtype, int root,
+                        const dlbb_view_t* in_view, void* stream);
+/* The same on lists of tensors: in_ptrs[p] goes to rank p, out_ptrs[r] comes from rank r (bytes_per_peer bytes each);
+ * packed and unpacked inside the kernel, no flattening copies. */
+int dlbb_alltoall_ptrs(dlbb_comm_t* c, const void* const* in_ptrs, void* const* out_ptrs, int64_t bytes_per_peer,
+                       void* stream);
 /* Point-to-point: send `send_count` elements to send_peer and / or receive `recv_count` from
  * recv_peer in one kernel (ring sendrecv, ref collectives/1d/openmpi.py:173-198; plain send / recv
  * with the other peer = -1, ref test/test_deepseed.py:132-153).  Only the ranks involved call it.

@@ -46,7 +46,8 @@ def setenv(**kw):
 arena_a, _ = comm.alloc(MAXB // 2 + 4096, bf)      # in-place tensor
 arena_b, _ = comm.alloc(MAXB // 2 + 4096, bf)      # second tensor (reduce-scatter output etc.)
 TOL = {torch.bfloat16: 2e-2, torch.float32: 1e-5}
-VARIANTS = [("mc", dict(DLBB_MC_ALLREDUCE=1, DLBB_MC_REDUCE=1, DLBB_MC_REDUCE_SCATTER=1, DLBB_BCAST_MC=1, DLBB_MC_WORLD2=1)),
+os.environ.setdefault("DLBB_SYMM_MIN_BYTES", "1")   # this tool exercises the direct kernels at every size
+VARIANTS = [("mc", dict(DLBB_MC_ALLREDUCE=1, DLBB_MC_REDUCE=1, DLBB_MC_REDUCE_SCATTER=1, DLBB_BCAST_MC=1, DLBB_MC_WORLD2=1, DLBB_BCAST_MC_MAX_BYTES=1 << 40)),
             ("p2p", dict(DLBB_MC_ALLREDUCE=0, DLBB_MC_REDUCE=0, DLBB_MC_REDUCE_SCATTER=0, DLBB_BCAST_MC=0, DLBB_MC_WORLD2=0))]
 try:
     for vname, env in (VARIANTS if os.environ.get("SYMM_SKIP_NUMERICS") != "1" else []):

@@ -1,6 +1,8 @@
 #!/usr/bin/env python3
 """Per-kernel count of the SASS mnemonics that prove the Blackwell paths (B200_PROFILING.md):
-UTC*MMA = tcgen05.mma, LDTM = tcgen05.ld, UTMALDG/UTMASTG = TMA, MULTIMEM/*.MMA? = multimem, SYNCS = mbarrier."""
+UTC*MMA = tcgen05.mma, LDTM = tcgen05.ld, UTMALDG/UTMASTG = TMA, LDGMC = multimem.ld_reduce, SYNCS = mbarrier.
+multimem.st has no mnemonic of its own: it lowers to STG.E.128.STRONG.SYS on a multicast address (the same encoding as
+st.relaxed.sys), counted here as STG.SYS; the kernels' ordinary stores are weak and count as STG."""
 import collections, re, subprocess, sys
 lib = sys.argv[1] if len(sys.argv) > 1 else "distributed_llm_backend_benchmark_b200/lib/libdlbb.so"
 out = subprocess.run(["cuobjdump", "-sass", lib], capture_output=True, text=True).stdout
