@@ -143,10 +143,41 @@ __device__ __forceinline__ void grid_scatter_view(char* dst, const ViewDev& ov, 
     int64_t done = 0;
     if (vec) {
         const int64_t nvec = bytes >> 4;
-        for (int64_t i = tid; i < nvec; i += nth) st_v4(dst + view_byte_off(ov, es, b0 + (i << 4)), ld_peer_v4(src + (i << 4)));
+        for (int64_t i0 = tid; i0 < nvec; i0 += nth * 4) {
+            uint4 t[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+                if (i0 + u * nth < nvec) t[u] = ld_peer_v4(src + ((i0 + u * nth) << 4));
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+                if (i0 + u * nth < nvec) st_v4(dst + view_byte_off(ov, es, b0 + ((i0 + u * nth) << 4)), t[u]);
+        }
         done = nvec << 4;
     }
     for (int64_t b = done + tid; b < bytes; b += nth) dst[view_byte_off(ov, es, b0 + b)] = ld_peer_scalar(src + b);
+}
+
+// Whole grid: gather `bytes` logical bytes of a strided local source, starting at logical byte offset b0 of the view,
+// into dense (staging) memory.
+__device__ __forceinline__ void grid_gather_view(char* dst, const char* src, const ViewDev& v, int es, int64_t b0, int64_t bytes) {
+    const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t nth = (int64_t)gridDim.x * blockDim.x;
+    const bool vec = view_vec_ok_bytes(v, es, src) && (b0 & 15) == 0 && (reinterpret_cast<uintptr_t>(dst) & 15) == 0;
+    int64_t done = 0;
+    if (vec) {
+        const int64_t nvec = bytes >> 4;
+        for (int64_t i0 = tid; i0 < nvec; i0 += nth * 4) {
+            uint4 t[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+                if (i0 + u * nth < nvec) t[u] = ld_stream_v4(src + view_byte_off(v, es, b0 + ((i0 + u * nth) << 4)));
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+                if (i0 + u * nth < nvec) st_v4(dst + ((i0 + u * nth) << 4), t[u]);
+        }
+        done = nvec << 4;
+    }
+    for (int64_t b = done + tid; b < bytes; b += nth) dst[b] = src[view_byte_off(v, es, b0 + b)];
 }
 
 // ------------------------------------------------------------------------------------------
@@ -179,18 +210,8 @@ move_kernel(CommDev c, const char* __restrict__ src, char* __restrict__ dst, Pie
         if (view.ndim == 0) {
             grid_copy_bytes<false>(my_stage + pc.b_off, src + pc.a_off, pc.n);
         } else {
-            // strided source: element-wise gather (bytes of one element are contiguous)
-            const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-            const int64_t nth = (int64_t)gridDim.x * blockDim.x;
-            const int64_t nel = pc.n / elem_size, e0 = pc.a_off / elem_size;
-            for (int64_t e = tid; e < nel; e += nth) {
-                const char* s = src + view_offset(view, e0 + e) * elem_size;
-                char* d = my_stage + pc.b_off + e * elem_size;
-                if (elem_size == 2) *reinterpret_cast<uint16_t*>(d) = *reinterpret_cast<const uint16_t*>(s);
-                else if (elem_size == 4) *reinterpret_cast<uint32_t*>(d) = *reinterpret_cast<const uint32_t*>(s);
-                else if (elem_size == 8) *reinterpret_cast<uint64_t*>(d) = *reinterpret_cast<const uint64_t*>(s);
-                else for (int b = 0; b < elem_size; ++b) d[b] = s[b];
-            }
+            // strided source: gathered here, 16 bytes at a time when the view's inner dimension allows it
+            grid_gather_view(my_stage + pc.b_off, src, view, elem_size, pc.a_off, pc.n);
         }
     }
     grid_barrier(c, bank, gridDim.x, epoch);
@@ -2067,6 +2088,23 @@ int dlbb_allgather_ptrs(dlbb_comm_t* c, const void* in, void* const* out_ptrs, i
     const ViewDev view = make_view(in_view);
     const bool receiver = root < 0 || c->rank == root;
     char* out0 = receiver ? static_cast<char*>(out_ptrs[0]) : nullptr;
+    if (view.ndim == 0) {   // zero-copy: the receivers pull every rank's input tensor straight into their list
+        PeerView pv;
+        bool zc = false;
+        const int rc = try_zero_copy(c, in, total, total * c->world, &pv, &zc, in);
+        if (rc) return rc;
+        if (zc) {
+            PieceList pull{};
+            if (receiver) {
+                pull.count = c->world;
+                for (int i = 0; i < c->world; ++i) {
+                    const int p = (c->rank + i) % c->world;
+                    pull.p[i] = Piece{p, 0, static_cast<char*>(out_ptrs[p]) - out0, total};
+                }
+            }
+            return launch_move(c, in, out0, PieceList{}, pull, view, (int)es, total * c->world, static_cast<cudaStream_t>(stream), &pv);
+        }
+    }
     for (int64_t done = 0; done < total; done += cap) {
         const int64_t n = std::min(cap, total - done);
         PieceList pack{}, pull{};
