@@ -126,8 +126,6 @@ class DataParallelTrainer:
         """forward + backward + gradient averaging + Adam.  Returns the local loss (fp32 [1], on device)."""
         self.step_count += 1
         eng = self.engine
-        if self.comm is not None and self.world > 1:
-            self.comm.dp_step_begin()
         with nvtx_range(f"dp_step_{self.step_count}"):
             loss = eng.forward_backward(x, target, on_bucket_ready=self._on_bucket_ready if self.overlap else None)
         if self.overlap:
@@ -136,8 +134,6 @@ class DataParallelTrainer:
         else:
             for i in range(len(self.buckets)):
                 self._update_bucket(i)
-        if self.comm is not None and self.world > 1:
-            self.comm.dp_step_end()
         return loss
 
     def state_dict(self) -> dict:

@@ -44,6 +44,10 @@ _SIGS = {
     "dlbb_comm_zero_copy_min_bytes": (SZ, [VP]),
     "dlbb_barrier": (I, [VP, VP]),
     "dlbb_allreduce": (I, [VP, VP, VP, I64, I, I, I, C.POINTER(_View), VP]),
+    "dlbb_allreduce_v": (I, [VP, VP, VP, I64, I, I, I, C.POINTER(_View), C.POINTER(_View), VP]),
+    "dlbb_allreduce_multi": (I, [VP, C.POINTER(VP), C.POINTER(I64), I, I, I, VP]),
+    "dlbb_broadcast_v": (I, [VP, VP, I64, I, I, C.POINTER(_View), VP]),
+    "dlbb_reduce_v": (I, [VP, VP, VP, I64, I, I, I, C.POINTER(_View), C.POINTER(_View), VP]),
     "dlbb_allreduce_residual_bf16": (I, [VP, VP, VP, VP, I64, VP]),
     "dlbb_reduce_scatter": (I, [VP, VP, VP, I64, I, I, VP]),
     "dlbb_allgather": (I, [VP, VP, VP, I64, I, C.POINTER(_View), VP]),
@@ -182,9 +186,13 @@ class SymmComm:
         """In place by default.  A non-contiguous input (<= 4 dims) is packed inside the kernel; the result is
         then written to `out` (contiguous), which is required in that case."""
         view = _strided_view(t)
+        if out is None and view is not None:
+            # in place on the strided view: gathered by the kernel's pack phase, scattered back by its unpack phase
+            _lib.check(self.lib.dlbb_allreduce_v(self.h, t.data_ptr(), t.data_ptr(), t.numel(), DTYPES[t.dtype], OPS[op],
+                                                 ALGOS[algo], C.byref(view), C.byref(view), _stream(self.device)),
+                       "allreduce (strided)")
+            return t
         if out is None:
-            if view is not None:
-                raise ValueError("all_reduce of a strided view needs a contiguous `out`")
             out = t
         assert out.is_contiguous() and out.numel() == t.numel()
         _lib.check(self.lib.dlbb_allreduce(self.h, t.data_ptr(), out.data_ptr(), t.numel(), DTYPES[t.dtype], OPS[op],
@@ -213,8 +221,23 @@ class SymmComm:
                    "allgather")
         return out
 
+    def all_reduce_multi(self, tensors: list[torch.Tensor], op: str = "sum") -> None:
+        """Bucket fusion: all-reduce many (small) contiguous tensors of one dtype in place with one launch per bucket."""
+        if not tensors:
+            return
+        dt = tensors[0].dtype
+        assert all(t.dtype == dt and t.is_contiguous() for t in tensors)
+        ptrs = (VP * len(tensors))(*[t.data_ptr() for t in tensors])
+        counts = (I64 * len(tensors))(*[t.numel() for t in tensors])
+        _lib.check(self.lib.dlbb_allreduce_multi(self.h, ptrs, counts, len(tensors), DTYPES[dt], OPS[op],
+                                                 _stream(self.device)), "allreduce_multi")
+
     def broadcast(self, t: torch.Tensor, root: int = 0):
-        assert t.is_contiguous()
+        view = _strided_view(t)
+        if view is not None:   # the root gathers the view, the receivers scatter into theirs, all inside the kernel
+            _lib.check(self.lib.dlbb_broadcast_v(self.h, t.data_ptr(), t.numel(), DTYPES[t.dtype], root, C.byref(view),
+                                                 _stream(self.device)), "broadcast (strided)")
+            return t
         _lib.check(self.lib.dlbb_broadcast(self.h, t.data_ptr(), t.numel(), DTYPES[t.dtype], root,
                                            _stream(self.device)), "broadcast")
         return t
@@ -309,12 +332,6 @@ class SymmComm:
             self.h, gseg, pseg, elem_off, n, m.data_ptr(), v.data_ptr(), master.data_ptr() if master is not None else None,
             lr, beta1, beta2, eps, weight_decay, grad_scale, step, 1 if use_multicast else 0, _stream(self.device)),
             "fused_reduce_adam")
-
-    def dp_step_begin(self) -> None:
-        pass
-
-    def dp_step_end(self) -> None:
-        pass
 
 
 class SymmMatrix:
