@@ -321,32 +321,34 @@ class LLMEngine:
         for n, i in enumerate(reversed(range(L))):
             lv, gv = self.layers[i], self.glayers[i]
             # FFN
+            # (a matrix's bucket is announced only after the LAST kernel of this step that reads the matrix's parameters -
+            #  its dgrad GEMM - has been enqueued: the bucket kernel overwrites the parameters, on every rank)
             ops.matmul(a["a"][i], dx, transpose_a=True, out=gv.wdown)                       # dW_down = a^T dx3
-            announce(True)
             ops.matmul(dx, lv.wdown, transpose_b=True, epilogue="mul_dgelu", aux=a["z"][i], out=a["dz"])
-            ops.matmul(a["h2"][i], a["dz"], transpose_a=True, out=gv.wup)                    # dW_up = h2^T dz
             announce(True)
+            ops.matmul(a["h2"][i], a["dz"], transpose_a=True, out=gv.wup)                    # dW_up = h2^T dz
             ops.matmul(a["dz"], lv.wup, transpose_b=True, out=a["dh"])                       # dh2
+            announce(True)
             m2, r2 = a["st2"][i]
             dx2, _, _ = ops.layernorm_bwd(a["dh"], a["x2"][i], m2, r2, lv.ln2_g, dx, dx=spare, dgamma_out=gv.ln2_g,
                                           dbeta_out=gv.ln2_b)
             # "attention" + projections
             attn = a["qkv"][i][:, :H]
             ops.matmul(attn, dx2, transpose_a=True, out=gv.wo)                               # dW_o
-            announce(True)
             ops.matmul(dx2, lv.wo, transpose_b=True, out=a["dattn"])                         # d attn
+            announce(True)
             if self.dense_qkv_backward:
                 # what autograd would run: zero-padded d(qkv) through the full 3H-wide GEMMs
                 a["dqkv"][:, :H].copy_(a["dattn"])
                 ops.matmul(a["h1"][i], a["dqkv"], transpose_a=True, out=gv.wqkv)
-                announce(True)
                 ops.matmul(a["dqkv"], lv.wqkv, transpose_b=True, out=a["dh"])
+                announce(True)
             else:
                 # d(qkv) is structurally zero outside the first H columns, so only that block of
                 # dW_qkv is non-zero (the rest of the bucket stays at its initial zeros).
                 ops.matmul(a["h1"][i], a["dattn"], transpose_a=True, out=gv.wqkv[:, :H])
-                announce(True)
                 ops.matmul(a["dattn"], lv.wqkv[:, :H], transpose_b=True, out=a["dh"])
+                announce(True)
             m1, r1 = a["st1"][i]
             dx1, _, _ = ops.layernorm_bwd(a["dh"], xs[i], m1, r1, lv.ln1_g, dx2, dx=dx, dgamma_out=gv.ln1_g,
                                           dbeta_out=gv.ln1_b)
