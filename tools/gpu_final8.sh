@@ -5,6 +5,7 @@ NP=${1:-8}
 ROOT=$(cd "$(dirname "$0")/.." && pwd); cd "$ROOT"
 export PATH="$ROOT/bin:$PATH"
 OUT=gpurun_out/publish_np$NP; mkdir -p $OUT/tuning
+timeout 150 python -m pytest tests/test_gpu_distributed.py -x -q -k "dp_training" 2>&1 | tail -3
 export DLBB_SWEEP_ITERS=10 DLBB_SWEEP_WARMUP=3
 BATCH_3D=1,8,32 SEQ_3D=1,2048 MAX_MB_3D=600 BATCH_STRIDED=1,8 SEQ_STRIDED=1,2048 bash baseline/run_sweeps.sh $NP $OUT/sweeps > $OUT/run_sweeps.log 2>&1
 grep -E "rc=" $OUT/run_sweeps.log
