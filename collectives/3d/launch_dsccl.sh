@@ -5,7 +5,8 @@
 #
 #   CCL_ALLREDUCE=<algo>          -> DLBB_ALGO=auto|oneshot|twoshot|nvls      all-reduce algorithm
 #   CCL_WORKER_COUNT=<n>          -> DLBB_CTAS=<n>                            CTAs ("channels") per collective kernel
-#   CCL_FUSION / *_THRESHOLD      -> DLBB_FUSION=0|1, DLBB_FUSION_BYTES=<n>   small-tensor bucket fusion (DP engine)
+#   CCL_FUSION / *_THRESHOLD      -> DLBB_FUSION=0|1, DLBB_FUSION_BYTES=<n>   bucket fusion: all_reduce_coalesced / dlbb_allreduce_multi
+#                                                                            pack up to 96 tensors into ONE launch (csrc/collectives: reduce_multi_kernel)
 #   (message-size crossover)      -> DLBB_ONESHOT_MAX_BYTES=<n>
 #   CCL_LOG_LEVEL=debug           -> DLBB_LOG_LEVEL=debug
 # CCL_* variables that are set are translated below so old experiment scripts keep working.
