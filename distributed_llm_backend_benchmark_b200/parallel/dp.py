@@ -41,9 +41,11 @@ class DataParallelTrainer:
         self._overlap_ctas = int(_os.environ.get("DLBB_ADAM_OVERLAP_CTAS", "148"))
         self.skip_optimizer = _os.environ.get("DLBB_DEBUG_SKIP_OPT", "0") == "1"   # debugging aid, invalidates results
         if engine.bucket_mode is None:
-            # one bucket per weight matrix when the exchange overlaps backward (it then starts a GEMM earlier and the
-            # exposed tail after the last layer is a quarter of a layer), one per layer when the optimizer runs afterwards
-            engine.bucket_mode = "matrix" if self.overlap else "layer"
+            # One bucket per layer.  Per-matrix buckets (DLBB_DP_BUCKETS=matrix: the exchange of dW_down starts while dW_up
+            # is still being computed) were measured and lost on 8 GPUs: every bucket kernel begins and ends with a barrier
+            # across all ranks, 161 instead of 33 of them per step cost more in waiting CTAs beside the GEMMs than the
+            # earlier start gains (139.7 ms / step vs 131.2; on 2 GPUs 141.7 vs ~143.5) - profiles/step_breakdown.md.
+            engine.bucket_mode = "layer"
         self.buckets = engine.bucket_slices()
         # Optimizer state is sharded: rank r owns elements [r*shard, (r+1)*shard) of every bucket
         # (buckets are padded up to a multiple of world*8 elements on the comm side).
