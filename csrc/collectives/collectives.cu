@@ -68,16 +68,20 @@ __device__ __forceinline__ bool view_vec_ok(const ViewDev& v, const void* base) 
     return ok;
 }
 // Store vector i (elements [i*VE, (i+1)*VE) of the logical, dense order) into a dense or strided destination.
+// (the element-wise fall-back is kept out of line: it is the slow path, and inlined into every unrolled store site its
+//  four 64-bit divisions per element dominated the size and the compile time of the reduction kernels)
+template <typename T>
+__device__ __noinline__ void store_view_elems(T* dst, const ViewDev& v, int64_t i, uint4 o) {
+    constexpr int VE = 16 / sizeof(T);
+    const T* ot = reinterpret_cast<const T*>(&o);
+#pragma unroll 1
+    for (int e = 0; e < VE; ++e) dst[view_offset(v, i * VE + e)] = ot[e];
+}
 template <typename T>
 __device__ __forceinline__ void store_view_vec(T* __restrict__ dst, const ViewDev& v, int64_t i, const uint4& o, bool vec_ok) {
     constexpr int VE = 16 / sizeof(T);
-    if (vec_ok) {
-        st_v4(dst + view_offset(v, i * VE), o);
-    } else {
-        const T* ot = reinterpret_cast<const T*>(&o);
-#pragma unroll
-        for (int e = 0; e < VE; ++e) dst[view_offset(v, i * VE + e)] = ot[e];
-    }
+    if (vec_ok) st_v4(dst + view_offset(v, i * VE), o);
+    else store_view_elems<T>(dst, v, i, o);
 }
 
 // Copy `bytes` bytes with the whole grid.  16-byte vectors when everything is aligned.
@@ -120,19 +124,25 @@ __device__ __forceinline__ bool view_vec_ok_bytes(const ViewDev& v, int es, cons
     return ok;
 }
 // 16 logical bytes starting at logical byte offset b (a multiple of 16) of a dense or strided local buffer
-__device__ __forceinline__ uint4 ld_view_v4(const char* base, const ViewDev& v, int es, int64_t b, bool vec_ok) {
-    if (vec_ok) return ld_stream_v4(base + view_byte_off(v, es, b));
+__device__ __noinline__ uint4 ld_view_bytes(const char* base, const ViewDev& v, int es, int64_t b) {   // slow path, out of line
     uint4 r;
     char* rb = reinterpret_cast<char*>(&r);
-#pragma unroll
+#pragma unroll 1
     for (int k = 0; k < 16; ++k) rb[k] = base[view_byte_off(v, es, b + k)];
     return r;
 }
-__device__ __forceinline__ void st_view_v4(char* base, const ViewDev& v, int es, int64_t b, const uint4& val, bool vec_ok) {
-    if (vec_ok) { st_v4(base + view_byte_off(v, es, b), val); return; }
+__device__ __noinline__ void st_view_bytes(char* base, const ViewDev& v, int es, int64_t b, uint4 val) {
     const char* vb = reinterpret_cast<const char*>(&val);
-#pragma unroll
+#pragma unroll 1
     for (int k = 0; k < 16; ++k) base[view_byte_off(v, es, b + k)] = vb[k];
+}
+__device__ __forceinline__ uint4 ld_view_v4(const char* base, const ViewDev& v, int es, int64_t b, bool vec_ok) {
+    if (vec_ok) return ld_stream_v4(base + view_byte_off(v, es, b));
+    return ld_view_bytes(base, v, es, b);
+}
+__device__ __forceinline__ void st_view_v4(char* base, const ViewDev& v, int es, int64_t b, const uint4& val, bool vec_ok) {
+    if (vec_ok) st_v4(base + view_byte_off(v, es, b), val);
+    else st_view_bytes(base, v, es, b, val);
 }
 // Whole grid: copy `bytes` logical bytes from a peer's (dense) staging into a strided local destination, starting at
 // logical byte offset b0 of the view.

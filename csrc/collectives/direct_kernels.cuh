@@ -269,25 +269,27 @@ static int launch_direct_T(dlbb_comm* c, const DirectPlan& pl, cudaStream_t s, i
     c->epoch[0] += 2;
     const int ctas = direct_ctas(c, bytes);
     const bool mc = pl.mc_src && MmReduce<T>::ok && OP == DLBB_SUM;
-#define DLBB_DIRECT_LAUNCH(MCS, SNK)                                                                              \
-    do {                                                                                                          \
-        if (MCS || c->world > 4) direct_reduce_kernel<T, OP, MCS, SNK, 8><<<ctas, kDirThreads, 0, s>>>(c->dev, pl.a, 0, ep); \
-        else if (c->world > 2) direct_reduce_kernel<T, OP, MCS, SNK, 4><<<ctas, kDirThreads, 0, s>>>(c->dev, pl.a, 0, ep);   \
-        else direct_reduce_kernel<T, OP, MCS, SNK, 2><<<ctas, kDirThreads, 0, s>>>(c->dev, pl.a, 0, ep);                      \
+    // (instantiations are limited to what the entry points use: a multimem source ignores MAXW; peer sources never feed a
+    //  multimem sink)
+#define DLBB_DIRECT_P2P(SNK)                                                                                        \
+    do {                                                                                                            \
+        if (c->world > 4) direct_reduce_kernel<T, OP, false, SNK, 8><<<ctas, kDirThreads, 0, s>>>(c->dev, pl.a, 0, ep);      \
+        else if (c->world > 2) direct_reduce_kernel<T, OP, false, SNK, 4><<<ctas, kDirThreads, 0, s>>>(c->dev, pl.a, 0, ep); \
+        else direct_reduce_kernel<T, OP, false, SNK, 2><<<ctas, kDirThreads, 0, s>>>(c->dev, pl.a, 0, ep);                   \
     } while (0)
     if constexpr (MmReduce<T>::ok && OP == DLBB_SUM) {
         if (mc) {
-            if (pl.sink == SINK_ONE) DLBB_DIRECT_LAUNCH(true, SINK_ONE);
-            else if (pl.sink == SINK_MC) DLBB_DIRECT_LAUNCH(true, SINK_MC);
-            else DLBB_DIRECT_LAUNCH(true, SINK_ALL);
+            if (pl.sink == SINK_ONE) direct_reduce_kernel<T, OP, true, SINK_ONE, 8><<<ctas, kDirThreads, 0, s>>>(c->dev, pl.a, 0, ep);
+            else if (pl.sink == SINK_MC) direct_reduce_kernel<T, OP, true, SINK_MC, 8><<<ctas, kDirThreads, 0, s>>>(c->dev, pl.a, 0, ep);
+            else direct_reduce_kernel<T, OP, true, SINK_ALL, 8><<<ctas, kDirThreads, 0, s>>>(c->dev, pl.a, 0, ep);
             DLBB_CHECK_LAUNCH("direct_reduce_kernel (multimem)");
             return 0;
         }
     }
-    if (pl.sink == SINK_ONE) DLBB_DIRECT_LAUNCH(false, SINK_ONE);
-    else if (pl.sink == SINK_MC) DLBB_DIRECT_LAUNCH(false, SINK_MC);
-    else DLBB_DIRECT_LAUNCH(false, SINK_ALL);
-#undef DLBB_DIRECT_LAUNCH
+    if (pl.sink == SINK_MC) { set_error("direct reduce: a multimem sink needs a multimem source"); return -2; }
+    if (pl.sink == SINK_ONE) DLBB_DIRECT_P2P(SINK_ONE);
+    else DLBB_DIRECT_P2P(SINK_ALL);
+#undef DLBB_DIRECT_P2P
     DLBB_CHECK_LAUNCH("direct_reduce_kernel");
     return 0;
 }
