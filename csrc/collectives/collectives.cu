@@ -16,18 +16,12 @@
 #include "../../include/dlbb.h"
 #include "../../include/dlbb_comm.h"
 #include "coll_device.cuh"
+#include "view_math.h"
 
 namespace dlbb {
 
 constexpr int kCollThreads = 256;
 constexpr int kU = 8;   // independent 16 B requests a thread keeps in flight (NVLink latency ~2 us)
-
-struct ViewDev {
-    int ndim;            // 0 = contiguous
-    int64_t size[4];
-    int64_t stride[4];
-    int64_t base;        // logical element offset added to every index (a launch that covers a later part of the view)
-};
 
 struct Piece {           // a contiguous run of elements / bytes
     int peer;            // pull: whose staging to read (pack: unused)
@@ -41,32 +35,6 @@ struct PieceList {
     Piece p[DLBB_MAX_RANKS];
 };
 
-__device__ __forceinline__ int64_t view_offset(const ViewDev& v, int64_t idx) {
-    if (v.ndim == 0) return idx;
-    idx += v.base;
-    int64_t off = 0;
-#pragma unroll
-    for (int d = 3; d >= 0; --d) {
-        if (d < v.ndim) {
-            const int64_t q = idx / v.size[d];
-            off += (idx - q * v.size[d]) * v.stride[d];
-            idx = q;
-        }
-    }
-    return off;
-}
-
-// A strided destination (K12, unpack side): can 16-byte vectors of T be stored with one index decomposition each?
-// (innermost dimension dense and a whole number of vectors, every other stride and the base pointer vector aligned)
-template <typename T>
-__device__ __forceinline__ bool view_vec_ok(const ViewDev& v, const void* base) {
-    constexpr int VE = 16 / sizeof(T);
-    if (v.ndim == 0) return (reinterpret_cast<uintptr_t>(base) & 15) == 0;
-    const int last = v.ndim - 1;
-    bool ok = v.stride[last] == 1 && v.size[last] % VE == 0 && v.base % VE == 0 && (reinterpret_cast<uintptr_t>(base) & 15) == 0;
-    for (int d = 0; d < last; ++d) ok = ok && (v.stride[d] % VE == 0);
-    return ok;
-}
 // Store vector i (elements [i*VE, (i+1)*VE) of the logical, dense order) into a dense or strided destination.
 // (the element-wise fall-back is kept out of line: it is the slow path, and inlined into every unrolled store site its
 //  four 64-bit divisions per element dominated the size and the compile time of the reduction kernels)
@@ -109,20 +77,6 @@ __device__ __forceinline__ void grid_copy_bytes(char* dst, const char* src, int6
 }
 
 // ---- byte-typed view access for the data-movement kernels (element size known only at run time)
-__device__ __forceinline__ int64_t view_byte_off(const ViewDev& v, int es, int64_t b) {   // logical byte -> byte in the view
-    if (v.ndim == 0) return b;
-    const int64_t e = b / es;
-    return view_offset(v, e) * es + (b - e * es);
-}
-__device__ __forceinline__ bool view_vec_ok_bytes(const ViewDev& v, int es, const void* base) {
-    if ((reinterpret_cast<uintptr_t>(base) & 15) != 0) return false;
-    if (v.ndim == 0) return true;
-    if (es > 16 || 16 % es != 0) return false;
-    const int VE = 16 / es, last = v.ndim - 1;
-    bool ok = v.stride[last] == 1 && v.size[last] % VE == 0;
-    for (int d = 0; d < last; ++d) ok = ok && (v.stride[d] % VE == 0);
-    return ok;
-}
 // 16 logical bytes starting at logical byte offset b (a multiple of 16) of a dense or strided local buffer
 __device__ __noinline__ uint4 ld_view_bytes(const char* base, const ViewDev& v, int es, int64_t b) {   // slow path, out of line
     uint4 r;
