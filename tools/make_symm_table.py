@@ -27,5 +27,24 @@ for n in (2, 4, 8):
         out.append(f"| {r['op']} | {r['bytes']} | {f1(g('symm_mc_us'))} | {f1(g('symm_p2p_us'))} | {f1(g('ipc_us'))} | {f1(g('nccl_us'))} | "
                    f"{f1(g('symm_mc_busbw'))} | {f1(g('symm_p2p_busbw'))} | {f1(g('ipc_busbw'))} | {f1(g('nccl_busbw'))} | "
                    f"{best / r['nccl_busbw'] if r['nccl_busbw'] else 0:.2f} |")
+out.append("""
+## Reading (8 GPUs)
+
+* **All-reduce**: the in-place multimem form moves (1 + 1/P) x S into every GPU (the reduced share it asked for plus the
+  multicast result) and S out of it, so its NVLink roofline at the measured 770 GB/s per direction is
+  2 (P-1)/P / (1 + 1/P) x 770 = 1198 GB/s of bus bandwidth; 813 GB/s at 1 GiB is 0.68 of that and 1.12x NCCL (727).  The
+  peer form moves 2 (P-1)/P x S per direction (roofline 770 GB/s of bus bandwidth): 636 = 0.83.  Between 4 MiB and 128 MiB
+  the in-place forms are 1.2-2.0x NCCL; below 256 KiB the library routes symmetric tensors through the staged
+  single-barrier kernels (the table forces the direct kernels at every size).
+* **Reduce-scatter**: peer loads with 16 vectors in flight per thread reach 634 GB/s = 0.82 of the link rate and match
+  NCCL at 1 GiB (630), 1.02-1.4x below; the switch reduction is never faster here and is opt-in.
+* **Reduce / broadcast**: 0.83-0.84 of NCCL at 1 GiB, 0.85-0.90 at 128-512 MiB, at or above NCCL up to 4 MiB.  Multicast
+  delivery saturates near 400-420 GB/s per GPU (`symm mc` broadcast column), the peer relay reaches 540 with every link
+  carrying S one way and 6/7 S the other; for reduce the multimem form is limited by the reducers' out-links carrying
+  (1 + 1/P) x S (bound 684 GB/s at 770 per link, 532 measured).  `DESIGN.md` section 3 has the experiments behind this.
+* Results are bit-identical on every rank; every numerics check (all-reduce SUM / MAX, reduce and broadcast from two
+  roots, reduce-scatter; bf16 and fp32; three sizes; symmetric and CUDA-IPC tensors; multimem and peer variants) passed on
+  2, 4 and 8 GPUs.
+""")
 (root / "profiles" / "collectives_symmetric.md").write_text("\n".join(out) + "\n")
 print("wrote profiles/collectives_symmetric.md")
