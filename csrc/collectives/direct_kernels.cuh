@@ -15,6 +15,7 @@
 // collectives/1d/dsccl.py:59-163, collectives/3d/dsccl.py:46-118; reduce-scatter is the ZeRO-2 gradient exchange of
 // test/ccl.py:86-88.
 #pragma once
+#include "direct_math.h"
 
 namespace dlbb {
 
@@ -126,26 +127,20 @@ reduce_pull_kernel(CommDev c, const __grid_constant__ PeerView in, char* __restr
                    int64_t stage_off, uint32_t flag_base, int chunk_vecs, int bank, uint32_t epoch) {
     const int P = c.world;
     const int nred = MC_SRC ? P : P - 1;
-    const int my_j = MC_SRC ? c.rank : (c.rank - root - 1 + P) % P;    // my reducer index (P2P: the root gets P-1 = none)
+    const int my_j = MC_SRC ? c.rank : relay_index(c.rank, root, P);    // my reducer index (P2P: the root gets P-1 = none)
     const bool is_root = c.rank == root;
-    const int64_t share = (nvec + nred - 1) / nred;
     const int group = blockIdx.x / rows, row = blockIdx.x - group * rows;
-    const int nchunks = static_cast<int>((((share + rows - 1) / rows) + chunk_vecs - 1) / chunk_vecs);   // same everywhere
+    const int nchunks = share_nchunks(nvec, nred, rows, chunk_vecs);   // same everywhere
     row_barrier(c, bank, blockIdx.x, epoch);
-    auto row_range = [&](int j, int64_t& s_lo, int64_t& r_lo, int64_t& r_hi) {
-        s_lo = min((int64_t)j * share, nvec);
-        const int64_t s_hi = min(s_lo + share, nvec);
-        const int64_t per = (s_hi - s_lo + rows - 1) / rows;
-        r_lo = min(s_lo + (int64_t)row * per, s_hi);
-        r_hi = min(r_lo + per, s_hi);
-    };
+    auto row_range = [&](int j, int64_t& s_lo, int64_t& r_lo, int64_t& r_hi) { share_row_range(nvec, nred, rows, j, row, s_lo, r_lo, r_hi); };
     if (group == 0 && my_j < nred) {
         // ---- reduce my share; the root (multimem mode only) writes its share straight into its tensor
         int64_t s_lo, r_lo, r_hi;
         row_range(my_j, s_lo, r_lo, r_hi);
         char* stage = c.stage[c.rank] + stage_off;
         for (int k = 0; k < nchunks; ++k) {
-            const int64_t c_lo = min(r_lo + (int64_t)k * chunk_vecs, r_hi), c_hi = min(c_lo + chunk_vecs, r_hi);
+            int64_t c_lo, c_hi;
+            chunk_range(r_lo, r_hi, k, chunk_vecs, c_lo, c_hi);
             if (is_root) {
                 reduce_span<T, OP, MC_SRC, MAXW>(c, in, c_lo, c_hi, [&](int64_t i, const uint4& o) { st_v4(out + (i << 4), o); });
             } else {
@@ -158,12 +153,13 @@ reduce_pull_kernel(CommDev c, const __grid_constant__ PeerView in, char* __restr
     } else if (is_root && group >= (MC_SRC ? 1 : 0)) {
         // ---- the root pulls one reducer's share out of that reducer's staging
         const int j = MC_SRC ? (root + group) % P : group;              // reducer index served by this group
-        const int q = MC_SRC ? j : (root + 1 + j) % P;                  // its rank
+        const int q = MC_SRC ? j : relay_rank(j, root, P);              // its rank
         int64_t s_lo, r_lo, r_hi;
         row_range(j, s_lo, r_lo, r_hi);
         const char* from = c.stage[q] + stage_off;
         for (int k = 0; k < nchunks; ++k) {
-            const int64_t c_lo = min(r_lo + (int64_t)k * chunk_vecs, r_hi), c_hi = min(c_lo + chunk_vecs, r_hi);
+            int64_t c_lo, c_hi;
+            chunk_range(r_lo, r_hi, k, chunk_vecs, c_lo, c_hi);
             if (threadIdx.x == 0) wait_flag(pad_slot(c, root, kRelayBank, row, q), flag_base + k + 1, q, c.watchdog_ns);
             __syncthreads();
             for (int64_t i0 = c_lo + threadIdx.x; i0 < c_hi; i0 += (int64_t)blockDim.x * kU) {
@@ -195,19 +191,17 @@ __global__ void __launch_bounds__(kDirThreads)
 bcast_relay_kernel(CommDev c, const __grid_constant__ PeerView pv, int64_t nvec, int root, int rows, uint32_t flag_base,
                    int bank, uint32_t epoch, int kRelayChunkVecs) {
     const int P = c.world;
-    const int me = (c.rank - root - 1 + P) % P;          // relay index; P-1 = the root
+    const int me = relay_index(c.rank, root, P);         // relay index; P-1 = the root
     const bool is_root = c.rank == root;
-    const int64_t share = (nvec + (P - 1) - 1) / (P - 1);
     const int group = blockIdx.x / rows, row = blockIdx.x - group * rows;
     row_barrier(c, bank, blockIdx.x, epoch);
     if (!is_root) {
         // which relay's share this CTA moves: group 0 = mine (from the root), group g = the g-th other relay
-        const int j = group == 0 ? me : (me + group) % (P - 1);
-        const int owner = (root + 1 + j) % P;             // rank that relays share j
-        const int64_t s_lo = min((int64_t)j * share, nvec), s_hi = min(s_lo + share, nvec);
-        const int64_t per = (s_hi - s_lo + rows - 1) / rows;
-        const int64_t r_lo = min(s_lo + (int64_t)row * per, s_hi), r_hi = min(r_lo + per, s_hi);
-        const int nchunks = static_cast<int>((((share + rows - 1) / rows) + kRelayChunkVecs - 1) / kRelayChunkVecs);   // same everywhere
+        const int j = group == 0 ? me : other_relay(me, group, P);
+        const int owner = relay_rank(j, root, P);         // rank that relays share j
+        int64_t s_lo, r_lo, r_hi;
+        share_row_range(nvec, P - 1, rows, j, row, s_lo, r_lo, r_hi);
+        const int nchunks = share_nchunks(nvec, P - 1, rows, kRelayChunkVecs);   // same everywhere
         const char* from = group == 0 ? pv.ptr[root] : pv.ptr[owner];
         char* mine = pv.ptr[c.rank];
         if (MC) {
@@ -224,7 +218,8 @@ bcast_relay_kernel(CommDev c, const __grid_constant__ PeerView pv, int64_t nvec,
             }
         } else {
             for (int k = 0; k < nchunks; ++k) {
-                const int64_t c_lo = min(r_lo + (int64_t)k * kRelayChunkVecs, r_hi), c_hi = min(c_lo + kRelayChunkVecs, r_hi);
+                int64_t c_lo, c_hi;
+                chunk_range(r_lo, r_hi, k, kRelayChunkVecs, c_lo, c_hi);
                 if (group != 0) {
                     if (threadIdx.x == 0) wait_flag(pad_slot(c, c.rank, kRelayBank, row, owner), flag_base + k + 1, owner, c.watchdog_ns);
                     __syncthreads();
@@ -334,8 +329,7 @@ static int launch_reduce_pull_T(dlbb_comm* c, const PeerView& pv, void* out, int
         PeerView in = pv;
         for (int p = 0; p < P; ++p) in.ptr[p] = pv.ptr[p] + (done << 4);
         in.mc = pv.mc ? pv.mc + (done << 4) : nullptr;
-        const int64_t share = (n + nred - 1) / nred;
-        const uint32_t nchunks = static_cast<uint32_t>((((share + rows - 1) / rows) + chunk_vecs - 1) / chunk_vecs);
+        const uint32_t nchunks = static_cast<uint32_t>(share_nchunks(n, nred, rows, chunk_vecs));
         const uint32_t fb = c->epoch[kRelayBank];
         c->epoch[kRelayBank] += nchunks;
         const int64_t so = next_stage_off(c, s, false);
@@ -395,8 +389,7 @@ static int launch_bcast_relay(dlbb_comm* c, const PeerView& pv, int64_t nvec, in
     if (mc) rows = direct_ctas(c);
     else rows = std::max(1, (c->ctas > 0 ? std::min(c->ctas, kMaxCtas) : 294) / (P - 1));
     const int ctas = mc ? rows : rows * (P - 1);
-    const int64_t share = (nvec + (P - 1) - 1) / (P - 1);
-    const uint32_t nchunks = static_cast<uint32_t>((((share + rows - 1) / rows) + kRelayChunkVecs - 1) / kRelayChunkVecs);
+    const uint32_t nchunks = static_cast<uint32_t>(share_nchunks(nvec, P - 1, rows, kRelayChunkVecs));
     const uint32_t fb = c->epoch[kRelayBank];
     if (!mc) c->epoch[kRelayBank] += nchunks;
     const uint32_t ep = c->epoch[0] + 1;
