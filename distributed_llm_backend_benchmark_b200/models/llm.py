@@ -115,7 +115,7 @@ class LLMEngine:
         self.dense_qkv_backward = os.environ.get("DLBB_DENSE_QKV_BWD", "0") == "1"
         # Gradient buckets handed to the data-parallel engine: "matrix" = one per weight matrix, announced right after
         # that matrix's wgrad GEMM has been enqueued (the exchange of dW_down starts while dW_up is still being computed);
-        # "layer" = one per layer.  None = let the data-parallel engine choose (matrix when it overlaps, else layer).
+        # "layer" = one per layer.  None = let the data-parallel engine choose (it takes "layer": measured faster on 8 GPUs).
         self.bucket_mode = os.environ.get("DLBB_DP_BUCKETS")
         H, F, L = cfg.hidden_size, cfg.ffn_intermediate, cfg.num_layers
         self.layer_numel = cfg.params_per_layer(tp_size)
