@@ -1571,15 +1571,12 @@ int dlbb_reduce_v(dlbb_comm_t* c, const void* in, void* out, int64_t count, int 
             pl.a.in = pv;
             pl.a.out.ptr[0] = pv.ptr[root];
             pl.a.out_shift = 0;
-            if (pl.mc_src) {
-                const int64_t share = (nv + c->world - 1) / c->world;
-                pl.a.v_lo = std::min<int64_t>(c->rank * share, nv);
-                pl.a.v_hi = std::min<int64_t>(pl.a.v_lo + share, nv);
-            } else if (c->rank != root) {
-                const int64_t j = (c->rank - root - 1 + c->world) % c->world;
-                const int64_t share = (nv + c->world - 2) / (c->world - 1);
-                pl.a.v_lo = std::min<int64_t>(j * share, nv);
-                pl.a.v_hi = std::min<int64_t>(pl.a.v_lo + share, nv);
+            if (pl.mc_src) {          // P reducers, one share each (direct_math.h; rows = 1: the whole share)
+                int64_t s_lo;
+                share_row_range(nv, c->world, 1, c->rank, 0, s_lo, pl.a.v_lo, pl.a.v_hi);
+            } else if (c->rank != root) {   // P-1 reducers numbered from root+1
+                int64_t s_lo;
+                share_row_range(nv, c->world - 1, 1, relay_index(c->rank, root, c->world), 0, s_lo, pl.a.v_lo, pl.a.v_hi);
             }
             return launch_direct(c, dtype, op, pl, static_cast<cudaStream_t>(stream), bytes);
         }
