@@ -14,6 +14,12 @@ namespace dlbb {
 #define DLBB_WATCHDOG 1
 #endif
 
+#if defined(DLBB_HOST_EMU)
+}  // namespace dlbb
+#include "emu/cuda_emu.h"
+namespace dlbb {
+#include "emu/device_emu.h"   // host versions of the PTX helpers (flags, peer accesses, multimem)
+#else
 __device__ __forceinline__ void group_bar_sync(uint32_t id, uint32_t nthreads) {   // named barrier of a warp group
     asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
 }
@@ -52,6 +58,8 @@ __device__ __forceinline__ void wait_flag(const uint32_t* flag, uint32_t epoch, 
     }
 }
 
+#endif  // DLBB_HOST_EMU
+
 __device__ __forceinline__ uint32_t* pad_slot(const CommDev& c, int owner, int bank, int row, int col) {
     return c.pads[owner] + bank * kPadWordsPerBank + row * kPadStride + col;
 }
@@ -80,6 +88,7 @@ __device__ __forceinline__ void grid_barrier(const CommDev& c, int bank, int nro
     __syncthreads();
 }
 
+#if !defined(DLBB_HOST_EMU)
 // ------------------------------------------------------------------ coherent 16-byte accesses
 // Peer data produced during this kernel must not come from a stale L1 line: strong (relaxed,
 // system-scope) loads always go to the owner's L2.
@@ -139,6 +148,8 @@ __device__ __forceinline__ void mm_st_v4(void* mc, const uint4& v) {
                  "r"(v.z), "r"(v.w)
                  : "memory");
 }
+
+#endif  // !DLBB_HOST_EMU
 
 // ------------------------------------------------------------------ typed reduction
 template <typename T> struct Acc { using type = float; };
