@@ -207,6 +207,10 @@ broadcast_nvls_kernel(CommDev c, const char* __restrict__ src, char* __restrict_
     const char* mine = c.stage[c.rank] + stage_off;
     // (a strided tensor - the same view on every rank - is gathered by the root and scattered by the receivers here)
     const bool src_vec = view_vec_ok_bytes(view, es, src), dst_vec = view_vec_ok_bytes(view, es, dst);
+    // Everybody has entered this kernel - and so has left the previous one - before the root writes into their staging:
+    // the region this launch uses was the OUTPUT half of a preceding two-shot all-reduce, which a slower rank may still be
+    // unpacking (found by the host emulation under ThreadSanitizer: csrc/collectives/tests/emu_collectives_test.cpp).
+    row_barrier(c, bank, row, end_epoch - 1);
     for (int k = 0; k < nchunks; ++k) {
         const int64_t c_lo = std::min<int64_t>(v_lo + (int64_t)k * kBcChunkVecs, v_hi);
         const int64_t c_hi = std::min<int64_t>(c_lo + kBcChunkVecs, v_hi);
@@ -956,7 +960,10 @@ p2p_kernel(CommDev c, const char* __restrict__ send_src, int64_t send_bytes, int
     if (send_peer >= 0) {
         int64_t lo, hi;
         range(send_bytes, lo, hi);
-        if (threadIdx.x == 0) wait_flag(pad_slot(c, c.rank, kP2PBank, kP2PCtas + b, send_peer), send_epoch - 1, send_peer, c.watchdog_ns);
+        // The slot is free once EVERY CTA of the receiver has copied its part of the previous message: the byte ranges
+        // depend on the message length, so my range of this message may overlap other CTAs' ranges of the last one.
+        for (int t = threadIdx.x; t < (int)gridDim.x; t += blockDim.x)
+            wait_flag(pad_slot(c, c.rank, kP2PBank, kP2PCtas + t, send_peer), send_epoch - 1, send_peer, c.watchdog_ns);
         __syncthreads();
         cta_copy(c.stage[c.rank] + region_off + send_peer * slot_bytes + lo, send_src + lo, hi - lo, false);
         __syncthreads();
@@ -1773,13 +1780,13 @@ int dlbb_broadcast_v(dlbb_comm_t* c, void* buf, int64_t count, int dtype, int ro
             const int64_t n = std::min(cap, total - done);
             const int ctas = c->ctas > 0 ? std::min(c->ctas, kMaxCtas)
                                          : static_cast<int>(std::min<int64_t>(128, std::max<int64_t>(1, n / (64 << 10))));
-            // (not poisoned: the root may multicast into a receiver's staging before that receiver has entered the kernel)
-            const int64_t so = next_stage_off(c, s, false);
+            const int64_t so = next_stage_off(c, s);
             const int64_t per = ((n >> 4) + ctas - 1) / ctas;
             const int nchunks = static_cast<int>(std::max<int64_t>(1, (per + kBcChunkVecs - 1) / kBcChunkVecs));
             const uint32_t fb = c->epoch[kBcFlagBank];
             c->epoch[kBcFlagBank] += nchunks;
-            const uint32_t ep = ++c->epoch[0];
+            c->epoch[0] += 2;   // opening and closing barrier
+            const uint32_t ep = c->epoch[0];
             const int64_t ptr_off = view.ndim ? 0 : done;   // a strided tensor is addressed through the view from its base
             broadcast_nvls_kernel<<<ctas, kCollThreads, 0, s>>>(
                 c->dev, static_cast<const char*>(buf) + ptr_off, static_cast<char*>(buf) + ptr_off, n, root, so, fb, nchunks, 0, ep,

@@ -5,8 +5,15 @@
 inline void group_bar_sync(uint32_t id, uint32_t nthreads) { emu::tl_cta->bar[id & 15].sync(nthreads); }
 
 // ------------------------------------------------------------------ flags
+// (EMU_WEAK_FLAGS: negative control - flags without release / acquire semantics; the sanitizer must then report the data
+//  accesses that only the flags were ordering)
+#if defined(EMU_WEAK_FLAGS)
+inline void st_release_sys(uint32_t* p, uint32_t v) { __atomic_store_n(p, v, __ATOMIC_RELAXED); }
+inline uint32_t ld_acquire_sys(const uint32_t* p) { return __atomic_load_n(p, __ATOMIC_RELAXED); }
+#else
 inline void st_release_sys(uint32_t* p, uint32_t v) { __atomic_store_n(p, v, __ATOMIC_RELEASE); }
 inline uint32_t ld_acquire_sys(const uint32_t* p) { return __atomic_load_n(p, __ATOMIC_ACQUIRE); }
+#endif
 
 inline void wait_flag(const uint32_t* flag, uint32_t epoch, int peer, long long limit_ns) {
     long long t0 = 0;

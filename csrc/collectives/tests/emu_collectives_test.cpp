@@ -112,6 +112,382 @@ static void case_allreduce(World& w, int64_t n, int op, int algo, bool symm, boo
     });
 }
 
+// data-movement payloads: depend on the source rank, the index and the repetition; exact in bf16 (|v| <= 100)
+static inline double mval(int rank, int64_t i, int rep) { return static_cast<double>(((i * 7 + rank * 31 + rep * 3) % 201) - 100); }
+template <typename T>
+static void mfill(T* dst, int rank, int64_t n, int rep, int64_t i0 = 0) {
+    for (int64_t i = 0; i < n; ++i) dst[i] = from_d<T>(mval(rank, i0 + i, rep));
+}
+template <typename T>
+static bool expect_eq(const T* got, int64_t n, int src_rank, int rep, int64_t i0, int rank, const char* what) {
+    for (int64_t i = 0; i < n; ++i) {
+        const double e = mval(src_rank, i0 + i, rep), g = to_d(got[i]);
+        if (e != g) {
+            FAIL("%s: rank %d rep %d elem %lld (from rank %d): got %g expected %g", what, rank, rep, (long long)i, src_rank, g, e);
+            return false;
+        }
+    }
+    return true;
+}
+
+// ------------------------------------------------------------------ reduce-scatter / reduce
+template <typename T>
+static void case_reduce_scatter(World& w, int64_t cpr, int op, bool symm) {
+    char name[160];
+    snprintf(name, sizeof(name), "reduce_scatter %s %s cpr=%lld %s", DT<T>::name, op_name(op), (long long)cpr, symm ? "symm" : "plain");
+    g_case = name;
+    Bufs in(w, cpr * w.P * sizeof(T), symm), out(w, cpr * sizeof(T), symm);
+    w.run([&](int r, dlbb_comm* c) {
+        for (int rep = 0; rep < kReps; ++rep) {
+            fill(in.at<T>(r), r, cpr * w.P, rep);
+            CALL(dlbb_reduce_scatter(c, in.at<T>(r), out.at<T>(r), cpr, DT<T>::code, op, nullptr));
+            for (int64_t i = 0; i < cpr; ++i) {
+                const double e = reduce_expected(w.P, r * cpr + i, rep, op), g = to_d(out.at<T>(r)[i]);
+                if (e != g) { FAIL("rank %d rep %d elem %lld: got %g expected %g", r, rep, (long long)i, g, e); break; }
+            }
+            g_checks.fetch_add(1);
+        }
+    });
+}
+
+template <typename T>
+static void case_reduce(World& w, int64_t n, int op, int root, bool symm, bool inplace) {
+    char name[160];
+    snprintf(name, sizeof(name), "reduce %s %s n=%lld root=%d %s %s", DT<T>::name, op_name(op), (long long)n, root,
+             symm ? "symm" : "plain", inplace ? "inplace" : "outofplace");
+    g_case = name;
+    Bufs in(w, n * sizeof(T), symm), out(w, n * sizeof(T), symm);
+    w.run([&](int r, dlbb_comm* c) {
+        for (int rep = 0; rep < kReps; ++rep) {
+            T* src = in.at<T>(r);
+            T* dst = inplace ? src : out.at<T>(r);
+            fill(src, r, n, rep);
+            CALL(dlbb_reduce(c, src, dst, n, DT<T>::code, op, root, nullptr));
+            if (r == root)
+                for (int64_t i = 0; i < n; ++i) {
+                    const double e = reduce_expected(w.P, i, rep, op), g = to_d(dst[i]);
+                    if (e != g) { FAIL("root rep %d elem %lld: got %g expected %g", rep, (long long)i, g, e); break; }
+                }
+            g_checks.fetch_add(1);
+        }
+    });
+}
+
+// ------------------------------------------------------------------ all-gather / gather / scatter / broadcast / all-to-all
+template <typename T>
+static void case_allgather(World& w, int64_t cpr, bool symm) {
+    char name[160];
+    snprintf(name, sizeof(name), "allgather %s cpr=%lld %s", DT<T>::name, (long long)cpr, symm ? "symm" : "plain");
+    g_case = name;
+    Bufs in(w, cpr * sizeof(T), symm), out(w, cpr * w.P * sizeof(T), symm);
+    w.run([&](int r, dlbb_comm* c) {
+        for (int rep = 0; rep < kReps; ++rep) {
+            mfill(in.at<T>(r), r, cpr, rep);
+            CALL(dlbb_allgather(c, in.at<T>(r), out.at<T>(r), cpr, DT<T>::code, nullptr, nullptr));
+            for (int p = 0; p < w.P; ++p)
+                if (!expect_eq(out.at<T>(r) + p * cpr, cpr, p, rep, 0, r, "allgather")) break;
+            g_checks.fetch_add(1);
+        }
+    });
+}
+
+template <typename T>
+static void case_gather_scatter(World& w, int64_t n, int root, bool symm) {
+    char name[160];
+    snprintf(name, sizeof(name), "gather+scatter %s n=%lld root=%d %s", DT<T>::name, (long long)n, root, symm ? "symm" : "plain");
+    g_case = name;
+    Bufs small(w, n * sizeof(T), symm), big(w, n * w.P * sizeof(T), symm), back(w, n * sizeof(T), symm);
+    w.run([&](int r, dlbb_comm* c) {
+        for (int rep = 0; rep < kReps; ++rep) {
+            mfill(small.at<T>(r), r, n, rep);
+            CALL(dlbb_gather(c, small.at<T>(r), big.at<T>(r), n, DT<T>::code, root, nullptr));
+            if (r == root)
+                for (int p = 0; p < w.P; ++p)
+                    if (!expect_eq(big.at<T>(r) + p * n, n, p, rep, 0, r, "gather")) break;
+            // ... and back: the root scatters what it gathered
+            CALL(dlbb_scatter(c, big.at<T>(r), back.at<T>(r), n, DT<T>::code, root, nullptr));
+            expect_eq(back.at<T>(r), n, r, rep, 0, r, "scatter");
+            g_checks.fetch_add(2);
+        }
+    });
+}
+
+template <typename T>
+static void case_broadcast(World& w, int64_t n, int root, bool symm) {
+    char name[160];
+    snprintf(name, sizeof(name), "broadcast %s n=%lld root=%d %s", DT<T>::name, (long long)n, root, symm ? "symm" : "plain");
+    g_case = name;
+    Bufs buf(w, n * sizeof(T), symm);
+    w.run([&](int r, dlbb_comm* c) {
+        for (int rep = 0; rep < kReps; ++rep) {
+            if (r == root) mfill(buf.at<T>(r), root, n, rep);
+            else memset(buf.at<T>(r), 0x5a, n * sizeof(T));
+            CALL(dlbb_broadcast(c, buf.at<T>(r), n, DT<T>::code, root, nullptr));
+            expect_eq(buf.at<T>(r), n, root, rep, 0, r, "broadcast");
+            g_checks.fetch_add(1);
+        }
+    });
+}
+
+template <typename T>
+static void case_alltoall(World& w, int64_t cpr, bool symm) {
+    char name[160];
+    snprintf(name, sizeof(name), "alltoall %s cpr=%lld %s", DT<T>::name, (long long)cpr, symm ? "symm" : "plain");
+    g_case = name;
+    Bufs in(w, cpr * w.P * sizeof(T), symm), out(w, cpr * w.P * sizeof(T), symm);
+    w.run([&](int r, dlbb_comm* c) {
+        for (int rep = 0; rep < kReps; ++rep) {
+            // chunk p of my input: payload "from r" at logical offset p * cpr
+            mfill(in.at<T>(r), r, cpr * w.P, rep);
+            CALL(dlbb_alltoall(c, in.at<T>(r), out.at<T>(r), cpr, DT<T>::code, nullptr));
+            for (int p = 0; p < w.P; ++p)
+                if (!expect_eq(out.at<T>(r) + p * cpr, cpr, p, rep, r * cpr, r, "alltoall")) break;
+            g_checks.fetch_add(1);
+        }
+    });
+}
+
+// ------------------------------------------------------------------ point-to-point, fused residual, barrier
+template <typename T>
+static void case_ring_sendrecv(World& w, int64_t n) {
+    char name[160];
+    snprintf(name, sizeof(name), "sendrecv ring %s n=%lld", DT<T>::name, (long long)n);
+    g_case = name;
+    if (w.P < 2) return;
+    Bufs snd(w, n * sizeof(T), false), rcv(w, n * sizeof(T), false);
+    w.run([&](int r, dlbb_comm* c) {
+        const int next = (r + 1) % w.P, prev = (r + w.P - 1) % w.P;
+        for (int rep = 0; rep < kReps; ++rep) {
+            mfill(snd.at<T>(r), r, n, rep);
+            if (w.P == 2 && r == 1) {   // two ranks: one send and one receive each, in matching order
+                CALL(dlbb_sendrecv(c, nullptr, 0, -1, rcv.at<T>(r), n, prev, DT<T>::code, nullptr));
+                CALL(dlbb_sendrecv(c, snd.at<T>(r), n, next, nullptr, 0, -1, DT<T>::code, nullptr));
+            } else if (w.P == 2) {
+                CALL(dlbb_sendrecv(c, snd.at<T>(r), n, next, nullptr, 0, -1, DT<T>::code, nullptr));
+                CALL(dlbb_sendrecv(c, nullptr, 0, -1, rcv.at<T>(r), n, prev, DT<T>::code, nullptr));
+            } else {
+                CALL(dlbb_sendrecv(c, snd.at<T>(r), n, next, rcv.at<T>(r), n, prev, DT<T>::code, nullptr));
+            }
+            expect_eq(rcv.at<T>(r), n, prev, rep, 0, r, "sendrecv");
+            g_checks.fetch_add(1);
+        }
+    });
+}
+
+static void case_residual(World& w, int64_t n) {
+    char name[160];
+    snprintf(name, sizeof(name), "allreduce_residual bf16 n=%lld", (long long)n);
+    g_case = name;
+    using T = __nv_bfloat16;
+    Bufs in(w, n * sizeof(T), false), res(w, n * sizeof(T), false), out(w, n * sizeof(T), false);
+    w.run([&](int r, dlbb_comm* c) {
+        for (int rep = 0; rep < kReps; ++rep) {
+            fill(in.at<T>(r), r, n, rep);
+            for (int64_t i = 0; i < n; ++i) res.at<T>(r)[i] = from_d<T>(static_cast<double>((i + rep) % 3));
+            CALL(dlbb_allreduce_residual_bf16(c, in.at<T>(r), res.at<T>(r), out.at<T>(r), n, nullptr));
+            for (int64_t i = 0; i < n; ++i) {
+                const double e = reduce_expected(w.P, i, rep, DLBB_SUM) + static_cast<double>((i + rep) % 3), g = to_d(out.at<T>(r)[i]);
+                if (e != g) { FAIL("rank %d rep %d elem %lld: got %g expected %g", r, rep, (long long)i, g, e); break; }
+            }
+            g_checks.fetch_add(1);
+        }
+    });
+}
+
+static void case_barrier(World& w) {
+    g_case = "barrier";
+    // a barrier orders plain host-visible writes: every rank publishes a counter, barrier, reads all the others
+    static int slots[16];
+    w.run([&](int r, dlbb_comm* c) {
+        for (int rep = 1; rep <= kReps; ++rep) {
+            __atomic_store_n(&slots[r], rep, __ATOMIC_RELAXED);
+            CALL(dlbb_barrier(c, nullptr));
+            for (int p = 0; p < w.P; ++p)
+                if (__atomic_load_n(&slots[p], __ATOMIC_RELAXED) < rep) FAIL("rank %d passed barrier %d before rank %d arrived", r, rep, p);
+            CALL(dlbb_barrier(c, nullptr));
+            g_checks.fetch_add(1);
+        }
+    });
+}
+
+// ------------------------------------------------------------------ lists of tensors (K13 and the list collectives)
+template <typename T>
+static void case_multi(World& w, int tensors, int64_t n_each, int op) {
+    char name[160];
+    snprintf(name, sizeof(name), "allreduce_multi %s %s %d x %lld", DT<T>::name, op_name(op), tensors, (long long)n_each);
+    g_case = name;
+    std::vector<Bufs> bufs;
+    std::vector<int64_t> counts;
+    for (int t = 0; t < tensors; ++t) {
+        counts.push_back(n_each + (t % 3) * 5 + (t == 1 ? 0 : t));   // ragged sizes, some not a multiple of 16 bytes
+        bufs.emplace_back(w, counts.back() * sizeof(T), false);
+    }
+    w.run([&](int r, dlbb_comm* c) {
+        for (int rep = 0; rep < kReps; ++rep) {
+            std::vector<void*> ptrs;
+            for (int t = 0; t < tensors; ++t) {
+                T* b = bufs[t].at<T>(r);
+                for (int64_t i = 0; i < counts[t]; ++i) b[i] = from_d<T>(val(r, i + 11 * t, rep));
+                ptrs.push_back(b);
+            }
+            CALL(dlbb_allreduce_multi(c, ptrs.data(), counts.data(), tensors, DT<T>::code, op, nullptr));
+            for (int t = 0; t < tensors; ++t)
+                for (int64_t i = 0; i < counts[t]; ++i) {
+                    const double e = reduce_expected(w.P, i + 11 * t, rep, op), g = to_d(bufs[t].at<T>(r)[i]);
+                    if (e != g) { FAIL("rank %d rep %d tensor %d elem %lld: got %g expected %g", r, rep, t, (long long)i, g, e); t = tensors; break; }
+                }
+            g_checks.fetch_add(1);
+        }
+    });
+}
+
+template <typename T>
+static void case_ptrs(World& w, int64_t n, int root) {
+    char name[160];
+    snprintf(name, sizeof(name), "allgather_ptrs/alltoall_ptrs %s n=%lld root=%d", DT<T>::name, (long long)n, root);
+    g_case = name;
+    Bufs in(w, n * sizeof(T), false);
+    std::vector<Bufs> outs, a2a_in, a2a_out;
+    for (int p = 0; p < w.P; ++p) {
+        outs.emplace_back(w, n * sizeof(T), false);
+        a2a_in.emplace_back(w, n * sizeof(T), false);
+        a2a_out.emplace_back(w, n * sizeof(T), false);
+    }
+    w.run([&](int r, dlbb_comm* c) {
+        for (int rep = 0; rep < kReps; ++rep) {
+            mfill(in.at<T>(r), r, n, rep);
+            std::vector<void*> op(w.P), ao(w.P);
+            std::vector<const void*> ai(w.P);
+            for (int p = 0; p < w.P; ++p) {
+                op[p] = outs[p].at<T>(r);
+                memset(op[p], 0x11, n * sizeof(T));
+                mfill(a2a_in[p].at<T>(r), r, n, rep, 1000 * p);   // what rank r sends to rank p
+                ai[p] = a2a_in[p].at<T>(r);
+                ao[p] = a2a_out[p].at<T>(r);
+            }
+            CALL(dlbb_allgather_ptrs(c, in.at<T>(r), op.data(), n, DT<T>::code, root, nullptr, nullptr));
+            if (root < 0 || r == root)
+                for (int p = 0; p < w.P; ++p)
+                    if (!expect_eq(static_cast<T*>(op[p]), n, p, rep, 0, r, "allgather_ptrs")) break;
+            CALL(dlbb_alltoall_ptrs(c, ai.data(), ao.data(), n * (int64_t)sizeof(T), nullptr));
+            for (int p = 0; p < w.P; ++p)
+                if (!expect_eq(static_cast<T*>(ao[p]), n, p, rep, 1000 * r, r, "alltoall_ptrs")) break;
+            g_checks.fetch_add(2);
+        }
+    });
+}
+
+// ------------------------------------------------------------------ strided views (K12)
+struct TestView {
+    const char* name;
+    dlbb_view_t v;
+    int64_t count;      // logical elements
+    int64_t extent;     // elements of the underlying allocation
+};
+// [b, s, h] views of the kinds the 3-D sweeps pass (collectives/3d/*.py with DLBB_SWEEP_STRIDED=1) plus an element-wise one
+static std::vector<TestView> test_views(int64_t b, int64_t s, int64_t h) {
+    std::vector<TestView> out;
+    {   // last-dim slice of a wider tensor: [b, s, :h] of [b, s, h + 8]  (vector path)
+        TestView t{"slice", {3, {b, s, h, 0}, {s * (h + 8), h + 8, 1, 0}}, b * s * h, b * s * (h + 8)};
+        out.push_back(t);
+    }
+    {   // permuted batch / sequence: [s, b, h] view of a contiguous [b, s, h]  (vector path)
+        TestView t{"permute", {3, {s, b, h, 0}, {h, s * h, 1, 0}}, b * s * h, b * s * h};
+        out.push_back(t);
+    }
+    {   // transposed inner dims: [b, h, s] view of [b, s, h]  (element path)
+        TestView t{"transpose", {3, {b, h, s, 0}, {s * h, 1, h, 0}}, b * s * h, b * s * h};
+        out.push_back(t);
+    }
+    {   // every second row of a 2-D tensor, odd width (element path, 2 dims)
+        TestView t{"rows2", {2, {b * s, h - 1, 0, 0}, {2 * h, 1, 0, 0}}, b * s * (h - 1), 2 * b * s * h};
+        out.push_back(t);
+    }
+    return out;
+}
+static int64_t view_off(const dlbb_view_t& v, int64_t i) {   // independent of view_math.h: plain mixed-radix walk
+    int64_t idx[4] = {0, 0, 0, 0}, off = 0;
+    for (int d = v.ndim - 1; d >= 0; --d) { idx[d] = i % v.size[d]; i /= v.size[d]; }
+    for (int d = 0; d < v.ndim; ++d) off += idx[d] * v.stride[d];
+    return off;
+}
+static constexpr double kSentinel = 77.0;
+
+template <typename T>
+static void poison(T* base, int64_t extent) { for (int64_t i = 0; i < extent; ++i) base[i] = from_d<T>(kSentinel); }
+template <typename T>
+static void check_untouched(const T* base, const TestView& tv, int rank, const char* what) {
+    std::vector<char> in_view(tv.extent, 0);
+    for (int64_t i = 0; i < tv.count; ++i) in_view[view_off(tv.v, i)] = 1;
+    for (int64_t e = 0; e < tv.extent; ++e)
+        if (!in_view[e] && to_d(base[e]) != kSentinel) { FAIL("%s: rank %d wrote outside the view at element %lld", what, rank, (long long)e); return; }
+}
+
+template <typename T>
+static void case_views(World& w, int64_t b, int64_t s, int64_t h, bool symm) {
+    for (const TestView& tv : test_views(b, s, h)) {
+        char name[200];
+        snprintf(name, sizeof(name), "views %s %s [%lld,%lld,%lld] %s", DT<T>::name, tv.name, (long long)b, (long long)s, (long long)h,
+                 symm ? "symm" : "plain");
+        g_case = name;
+        Bufs t(w, tv.extent * sizeof(T), symm), dense(w, tv.count * w.P * sizeof(T), symm);
+        const int root = w.P - 1;
+        w.run([&](int r, dlbb_comm* c) {
+            T* base = t.at<T>(r);
+            T* flat = dense.at<T>(r);
+            for (int rep = 0; rep < 2; ++rep) {
+                // all-reduce in place on the view
+                poison(base, tv.extent);
+                for (int64_t i = 0; i < tv.count; ++i) base[view_off(tv.v, i)] = from_d<T>(val(r, i, rep));
+                CALL(dlbb_allreduce_v(c, base, base, tv.count, DT<T>::code, DLBB_SUM, DLBB_ALGO_AUTO, &tv.v, &tv.v, nullptr));
+                for (int64_t i = 0; i < tv.count; ++i) {
+                    const double e = reduce_expected(w.P, i, rep, DLBB_SUM), g = to_d(base[view_off(tv.v, i)]);
+                    if (e != g) { FAIL("allreduce_v rank %d rep %d elem %lld: got %g expected %g", r, rep, (long long)i, g, e); break; }
+                }
+                check_untouched(base, tv, r, "allreduce_v");
+                // strided -> contiguous all-reduce (pack only)
+                for (int64_t i = 0; i < tv.count; ++i) base[view_off(tv.v, i)] = from_d<T>(val(r, i, rep + 1));
+                CALL(dlbb_allreduce(c, base, flat, tv.count, DT<T>::code, DLBB_SUM, DLBB_ALGO_AUTO, &tv.v, nullptr));
+                for (int64_t i = 0; i < tv.count; ++i) {
+                    const double e = reduce_expected(w.P, i, rep + 1, DLBB_SUM), g = to_d(flat[i]);
+                    if (e != g) { FAIL("allreduce(view in) rank %d rep %d elem %lld: got %g expected %g", r, rep, (long long)i, g, e); break; }
+                }
+                // broadcast of the view
+                poison(base, tv.extent);
+                if (r == root) for (int64_t i = 0; i < tv.count; ++i) base[view_off(tv.v, i)] = from_d<T>(mval(root, i, rep));
+                CALL(dlbb_broadcast_v(c, base, tv.count, DT<T>::code, root, &tv.v, nullptr));
+                for (int64_t i = 0; i < tv.count; ++i) {
+                    const double e = mval(root, i, rep), g = to_d(base[view_off(tv.v, i)]);
+                    if (e != g) { FAIL("broadcast_v rank %d rep %d elem %lld: got %g expected %g", r, rep, (long long)i, g, e); break; }
+                }
+                check_untouched(base, tv, r, "broadcast_v");
+                // reduce to the root, in place on the view
+                poison(base, tv.extent);
+                for (int64_t i = 0; i < tv.count; ++i) base[view_off(tv.v, i)] = from_d<T>(val(r, i, rep));
+                CALL(dlbb_reduce_v(c, base, base, tv.count, DT<T>::code, DLBB_SUM, root, &tv.v, &tv.v, nullptr));
+                if (r == root) {
+                    for (int64_t i = 0; i < tv.count; ++i) {
+                        const double e = reduce_expected(w.P, i, rep, DLBB_SUM), g = to_d(base[view_off(tv.v, i)]);
+                        if (e != g) { FAIL("reduce_v rep %d elem %lld: got %g expected %g", rep, (long long)i, g, e); break; }
+                    }
+                    check_untouched(base, tv, r, "reduce_v");
+                }
+                // all-gather and gather with a strided input
+                for (int64_t i = 0; i < tv.count; ++i) base[view_off(tv.v, i)] = from_d<T>(mval(r, i, rep));
+                CALL(dlbb_allgather(c, base, flat, tv.count, DT<T>::code, &tv.v, nullptr));
+                for (int p = 0; p < w.P; ++p)
+                    if (!expect_eq(flat + p * tv.count, tv.count, p, rep, 0, r, "allgather(view in)")) break;
+                memset(flat, 0, tv.count * w.P * sizeof(T));
+                CALL(dlbb_gather_v(c, base, flat, tv.count, DT<T>::code, root, &tv.v, nullptr));
+                if (r == root)
+                    for (int p = 0; p < w.P; ++p)
+                        if (!expect_eq(flat + p * tv.count, tv.count, p, rep, 0, r, "gather_v")) break;
+                g_checks.fetch_add(6);
+            }
+        });
+    }
+}
+
 // ------------------------------------------------------------------ driver
 static bool want(const char* filter, const char* group) { return filter == nullptr || strstr(group, filter) != nullptr; }
 
@@ -142,6 +518,64 @@ int main(int argc, char** argv) {
             case_allreduce<float>(w, n, DLBB_SUM, DLBB_ALGO_DIRECT, false, true);
             case_allreduce<float>(w, n, DLBB_SUM, DLBB_ALGO_AUTO, false, true, 1);   // 4-byte aligned only
         }
+    }
+    const int roots[] = {0, P - 1, P / 2};
+    if (want(filter, "reduce_scatter"))
+        for (int64_t n : {4, 12, 300, 4100, 20000}) {
+            case_reduce_scatter<float>(w, n, DLBB_SUM, false);
+            case_reduce_scatter<__nv_bfloat16>(w, n * 2, DLBB_SUM, true);
+            case_reduce_scatter<int32_t>(w, n + 1, DLBB_MAX, false);
+        }
+    if (want(filter, "reduce "))
+        for (int64_t n : sizes)
+            for (int root : roots) {
+                case_reduce<float>(w, n, DLBB_SUM, root, false, true);
+                case_reduce<__nv_bfloat16>(w, n, DLBB_SUM, root, true, true);
+                case_reduce<float>(w, n, DLBB_SUM, root, false, false);
+                case_reduce<int64_t>(w, n, DLBB_MIN, root, false, true);
+            }
+    if (want(filter, "allgather"))
+        for (int64_t n : sizes) {
+            case_allgather<float>(w, n, false);
+            case_allgather<__nv_bfloat16>(w, n, true);
+            case_allgather<double>(w, n, false);
+        }
+    if (want(filter, "gather+scatter"))
+        for (int64_t n : {1, 300, 4099, 20000})
+            for (int root : roots) {
+                case_gather_scatter<float>(w, n, root, false);
+                case_gather_scatter<__nv_bfloat16>(w, n, root, true);
+            }
+    if (want(filter, "broadcast"))
+        for (int64_t n : sizes)
+            for (int root : roots) {
+                case_broadcast<float>(w, n, root, false);
+                case_broadcast<__nv_bfloat16>(w, n, root, true);
+            }
+    if (want(filter, "alltoall"))
+        for (int64_t n : {1, 16, 301, 4096, 9000}) {
+            case_alltoall<float>(w, n, false);
+            case_alltoall<__nv_bfloat16>(w, n, true);
+        }
+    if (want(filter, "sendrecv"))
+        for (int64_t n : sizes) case_ring_sendrecv<float>(w, n);
+    if (want(filter, "residual"))
+        for (int64_t n : {8, 4096, 70000}) case_residual(w, n);
+    if (want(filter, "barrier")) case_barrier(w);
+    if (want(filter, "multi")) {
+        case_multi<float>(w, 5, 100, DLBB_SUM);
+        case_multi<__nv_bfloat16>(w, 16, 2048, DLBB_SUM);
+        case_multi<float>(w, 100, 40, DLBB_SUM);       // more tensors than one table holds
+        case_multi<int32_t>(w, 7, 9000, DLBB_MAX);     // more bytes than one bucket holds
+    }
+    if (want(filter, "ptrs"))
+        for (int64_t n : {5, 1024, 20000})
+            for (int root : {-1, 0, P - 1}) case_ptrs<float>(w, n, root);
+    if (want(filter, "views")) {
+        case_views<float>(w, 2, 5, 16, false);
+        case_views<__nv_bfloat16>(w, 3, 7, 24, false);
+        case_views<__nv_bfloat16>(w, 4, 33, 64, true);   // 16.5 KiB per rank: beyond the zero-copy threshold
+        case_views<float>(w, 4, 64, 96, false);          // 96 KiB per rank: sliced through the staging area
     }
     if (g_fail.load()) {
         printf("EMU COLLECTIVES FAILED: %d failures (world %d, %s)\n", g_fail.load(), P, mc ? "multicast" : "no multicast");

@@ -55,6 +55,7 @@ def main() -> int:
     ap.add_argument("--sanitize", default="none", choices=["none", "thread", "address"])
     ap.add_argument("--test", default=str(COLL / "tests" / "emu_collectives_test.cpp"))
     ap.add_argument("--opt", default="-O1")
+    ap.add_argument("--define", action="append", default=[], help="extra -D (e.g. EMU_WEAK_FLAGS: negative control)")
     a = ap.parse_args()
     out = Path(a.out)
     gen = out.parent / (out.name + "_src")
@@ -75,6 +76,7 @@ def main() -> int:
     assert total >= 20, f"only {total} kernel launches rewritten"
     flags = ["g++", "-std=c++17", a.opt, "-g", "-pthread", "-DDLBB_HOST_EMU", "-Wno-unknown-pragmas", "-Wno-unused-function",
              "-I/usr/local/cuda/include", f"-I{gen / 'csrc' / 'collectives'}", "-include", str(gen / "csrc" / "collectives" / "emu" / "cuda_emu.h")]
+    flags += [f"-D{d}" for d in a.define]
     if a.sanitize != "none":
         flags += [f"-fsanitize={a.sanitize}", "-fno-omit-frame-pointer"]
     srcs = [str(gen / "csrc" / "collectives" / u.replace(".cu", ".cpp")) for u in UNITS] + [a.test]
