@@ -1128,7 +1128,8 @@ static int launch_twoshot_T(dlbb_comm* c, bool nvls, const void* src, void* dst,
     const int64_t bytes = n * (int64_t)sizeof(T);
     const int64_t in_off = next_stage_off(c, s);
     const int64_t out_off = in_off == 0 ? static_cast<int64_t>(c->stage_bytes) : 0;
-    poison_region(c, out_off, s);   // the peers write my out-staging only after they have seen me enter this kernel
+    // (the out half is NOT poisoned here: a slower peer may still be reading it as the input half of the preceding
+    //  single-barrier kernel - the kernel itself first writes there after its first barrier, a host-side fill would not wait)
     const bool use_nvls = nvls && MmReduce<T>::ok && OP == DLBB_SUM;
     static const int64_t pipe_min = getenv("DLBB_PIPELINE_MIN_BYTES") ? atoll(getenv("DLBB_PIPELINE_MIN_BYTES")) : (8ll << 20);
     if (bytes >= pipe_min && use_nvls && root < 0) {
@@ -1569,7 +1570,8 @@ int dlbb_reduce_v(dlbb_comm_t* c, const void* in, void* out, int64_t count, int 
         if (zc) {
             const int64_t nv = bytes >> 4;
             const bool use_mc = pv.mc && nvls_ok && env_flag("DLBB_MC_REDUCE", true);
-            if (bytes >= (int64_t)(1 << 20) * 4 && env_flag("DLBB_REDUCE_PULL", false))
+            static const int64_t pull_min = getenv("DLBB_REDUCE_PULL_MIN_BYTES") ? atoll(getenv("DLBB_REDUCE_PULL_MIN_BYTES")) : (4ll << 20);
+            if (bytes >= pull_min && env_flag("DLBB_REDUCE_PULL", false))
                 return launch_reduce_pull(c, dtype, op, pv, out, nv, root, use_mc, static_cast<cudaStream_t>(stream));
             // small messages: one hop - the reducers store their share straight into the root's tensor
             DirectPlan pl{};

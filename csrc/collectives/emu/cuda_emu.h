@@ -32,7 +32,9 @@
 #include <atomic>
 #include <chrono>
 #include <condition_variable>
+#include <map>
 #include <mutex>
+#include <string>
 #include <thread>
 #include <vector>
 
@@ -82,6 +84,19 @@ inline std::atomic<long>& launches() {
     static std::atomic<long> n{0};
     return n;
 }
+// launches per kernel (the text of the launch expression), so that a test can tell which code paths a configuration took
+struct KernelCounts {
+    std::mutex m;
+    std::map<std::string, long> n;
+    void add(const char* name) {
+        std::lock_guard<std::mutex> lk(m);
+        ++n[name];
+    }
+};
+inline KernelCounts& kernel_counts() {
+    static KernelCounts k;
+    return k;
+}
 
 template <typename F>
 void run_grid(int grid, int block, F&& body) {
@@ -105,15 +120,17 @@ void run_grid(int grid, int block, F&& body) {
 
 template <typename K>
 struct Launcher {
+    const char* name;
     int grid, block;
     K kernel;
     template <typename... A>
     void operator()(A&&... a) const {
+        kernel_counts().add(name);
         run_grid(grid, block, [&] { kernel(a...); });
     }
 };
 template <typename K>
-Launcher<K> launcher(int grid, int block, K k) { return Launcher<K>{grid, block, k}; }
+Launcher<K> launcher(const char* name, int grid, int block, K k) { return Launcher<K>{name, grid, block, k}; }
 
 // ------------------------------------------------------------------ multicast windows
 struct McWindow {
@@ -140,7 +157,7 @@ inline long long now_ns() {
 
 }  // namespace emu
 
-#define EMU_LAUNCH(grid, block, ...) ::emu::launcher(static_cast<int>(grid), static_cast<int>(block), __VA_ARGS__)
+#define EMU_LAUNCH(grid, block, ...) ::emu::launcher(#__VA_ARGS__, static_cast<int>(grid), static_cast<int>(block), __VA_ARGS__)
 
 // the integer / floating-point min and max overloads that device code finds in the global namespace
 #define EMU_MINMAX(T)                                  \

@@ -169,6 +169,19 @@ int peer_registry_resolve(dlbb_comm* c, PeerRegistry*, const void* ptr, size_t b
 
 extern "C" {
 int dlbb_comm_has_multicast(const dlbb_comm_t* c) { return c->mc_supported ? 1 : 0; }
+// symmetric segments by id (the fused kernels take segment ids): index into the emulated box's segment list
+void* dlbb_symm_ptr(dlbb_comm_t*, int seg, int peer) {
+    emu::World& w = *emu::world();
+    return seg >= 0 && seg < (int)w.segs.size() && peer >= 0 && peer < w.P ? w.segs[seg].base[peer] : nullptr;
+}
+void* dlbb_symm_mc_ptr(dlbb_comm_t*, int seg) {
+    emu::World& w = *emu::world();
+    return seg >= 0 && seg < (int)w.segs.size() ? w.segs[seg].mc : nullptr;
+}
+size_t dlbb_symm_size(dlbb_comm_t*, int seg) {
+    emu::World& w = *emu::world();
+    return seg >= 0 && seg < (int)w.segs.size() ? w.segs[seg].size : 0;
+}
 const char* cudaGetErrorString(cudaError_t) { return "emulated"; }
 cudaError_t cudaGetLastError(void) { return cudaSuccess; }
 cudaError_t cudaMemsetAsync(void* p, int v, size_t n, cudaStream_t) {   // the rank's stream is its host thread: runs in order

@@ -177,12 +177,14 @@ extern "C" int dlbb_fused_reduce_adam_bf16(dlbb_comm_t* c, int grads_seg, int pa
     const uint32_t ep = c->epoch[kFusedBank] + 1;
     c->epoch[kFusedBank] += 2;
     cudaStream_t s = static_cast<cudaStream_t>(stream);
+#if !defined(DLBB_HOST_EMU)
     static bool carveout_set = false;
     if (!carveout_set) {  // co-reside with the GEMM CTAs: see csrc/kernels/optim.cu
         cudaFuncSetAttribute(fused_reduce_adam_kernel<true>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
         cudaFuncSetAttribute(fused_reduce_adam_kernel<false>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
         carveout_set = true;
     }
+#endif
     if (nvls)
         fused_reduce_adam_kernel<true><<<ctas, kFusedThreads, 0, s>>>(c->dev, pp, lo, hi, m, v, master, h, ep);
     else

@@ -12,6 +12,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <memory>
 #include <string>
 #include <vector>
 
@@ -87,7 +88,7 @@ static void fill(T* dst, int rank, int64_t n, int rep) {
     for (int64_t i = 0; i < n; ++i) dst[i] = from_d<T>(val(rank, i, rep));
 }
 
-static constexpr int kReps = 4;
+static const int kReps = getenv("EMU_REPS") ? atoi(getenv("EMU_REPS")) : 4;   // back-to-back repetitions of every call
 
 // ------------------------------------------------------------------ all-reduce
 template <typename T>
@@ -488,6 +489,184 @@ static void case_views(World& w, int64_t b, int64_t s, int64_t h, bool symm) {
     }
 }
 
+// ------------------------------------------------------------------ K20: fused gradient reduce + Adam + parameter broadcast
+static void ref_adam(float& w, float& m, float& v, float g_raw, float lr, float b1, float b2, float eps, float wd, float gs, int step) {
+    const float bc1_inv = static_cast<float>(1.0 / (1.0 - pow(static_cast<double>(b1), step)));
+    const float bc2_inv_sqrt = static_cast<float>(1.0 / sqrt(1.0 - pow(static_cast<double>(b2), step)));
+    float g = g_raw * gs;
+    if (wd != 0.f) g = fmaf(wd, w, g);
+    m = fmaf(b1, m, (1.f - b1) * g);
+    v = fmaf(b2, v, (1.f - b2) * g * g);
+    w -= lr * (m * bc1_inv) / (sqrtf(v) * bc2_inv_sqrt + eps);
+}
+
+static void case_fused_adam(World& w, int64_t n, int64_t elem_off, bool use_mc, bool with_master) {
+    char name[160];
+    snprintf(name, sizeof(name), "fused_adam n=%lld off=%lld %s %s", (long long)n, (long long)elem_off, use_mc ? "multimem" : "peer",
+             with_master ? "master" : "nomaster");
+    g_case = name;
+    using T = __nv_bfloat16;
+    const int P = w.P;
+    const size_t bytes = (elem_off + n) * sizeof(T);
+    w.alloc_symm((bytes + 255) / 256 * 256);
+    const int gseg = static_cast<int>(w.segs.size()) - 1;
+    w.alloc_symm((bytes + 255) / 256 * 256);
+    const int pseg = static_cast<int>(w.segs.size()) - 1;
+    const int64_t per = (n + P * 8 - 1) / (P * 8) * 8;
+    const float lr = 0.01f, b1 = 0.9f, b2 = 0.999f, eps = 1e-8f, wd = 0.01f, gs = 1.0f / P;
+    // expected trajectory of every element (fp32 state lives on the owning rank only; the arithmetic is the same everywhere)
+    std::vector<float> ew(n), em(n, 0.f), ev(n, 0.f);
+    for (int64_t i = 0; i < n; ++i) ew[i] = to_d(from_d<T>(0.25 * ((i % 9) - 4)));
+    std::vector<std::vector<float>> m(P), v(P), master(P);
+    for (int r = 0; r < P; ++r) {
+        const int64_t lo = std::min<int64_t>(r * per, n), hi = std::min<int64_t>(lo + per, n);
+        m[r].assign(per + 8, 0.f);
+        v[r].assign(per + 8, 0.f);
+        master[r].assign(per + 8, 0.f);
+        for (int64_t i = lo; i < hi; ++i) master[r][i - lo] = ew[i];
+        T* pr = reinterpret_cast<T*>(w.segs[pseg].base[r]) + elem_off;
+        for (int64_t i = 0; i < n; ++i) pr[i] = from_d<T>(ew[i]);
+    }
+    const int steps = 3;
+    std::vector<std::vector<float>> expect(steps, std::vector<float>(n));
+    for (int st = 1; st <= steps; ++st)
+        for (int64_t i = 0; i < n; ++i) {
+            float g = 0.f;
+            for (int r = 0; r < P; ++r) g += static_cast<float>(val(r, i, st));
+            // without fp32 master weights the update starts from the bf16 parameter
+            float wv = with_master ? ew[i] : static_cast<float>(to_d(from_d<T>(ew[i])));
+            ref_adam(wv, em[i], ev[i], g, lr, b1, b2, eps, wd, gs, st);
+            ew[i] = wv;
+            expect[st - 1][i] = static_cast<float>(to_d(from_d<T>(wv)));
+        }
+    w.run([&](int r, dlbb_comm* c) {
+        T* gr = reinterpret_cast<T*>(w.segs[gseg].base[r]) + elem_off;
+        const T* pr = reinterpret_cast<const T*>(w.segs[pseg].base[r]) + elem_off;
+        for (int st = 1; st <= steps; ++st) {
+            for (int64_t i = 0; i < n; ++i) gr[i] = from_d<T>(val(r, i, st));
+            CALL(dlbb_fused_reduce_adam_bf16(c, gseg, pseg, elem_off, n, m[r].data(), v[r].data(), with_master ? master[r].data() : nullptr,
+                                             lr, b1, b2, eps, wd, gs, st, use_mc ? 1 : 0, nullptr));
+            for (int64_t i = 0; i < n; ++i) {
+                const float g = static_cast<float>(to_d(pr[i])), e = expect[st - 1][i];
+                if (fabsf(g - e) > 0.008f * fabsf(e) + 1e-6f) {   // at most one bf16 ulp (rounding of an fp32 value on a tie)
+                    FAIL("rank %d step %d elem %lld: param %g expected %g", r, st, (long long)i, g, e);
+                    break;
+                }
+            }
+            g_checks.fetch_add(1);
+        }
+    });
+}
+
+// ------------------------------------------------------------------ mixed sequences
+// Different collectives back to back on one communicator, no host synchronisation in between: what one kernel leaves
+// behind in the staging halves / flag banks is what the next one starts from.  (Cases above join their rank threads
+// between calls of different kinds; here the only ordering between ranks is the kernels' own flag protocol.)
+static void case_mixed(World& w, unsigned seed, int length) {
+    char name[96];
+    snprintf(name, sizeof(name), "mixed seed=%u len=%d", seed, length);
+    g_case = name;
+    const int P = w.P;
+    const int64_t sizes[] = {5, 640, 4100, 20000};
+    struct Slot { Bufs a, b; Slot(World& w, size_t n, bool symm) : a(w, n, symm), b(w, n, symm) {} };
+    std::vector<std::unique_ptr<Slot>> plain, symm;
+    for (int64_t n : sizes) {
+        plain.emplace_back(new Slot(w, n * P * sizeof(float), false));
+        symm.emplace_back(new Slot(w, n * P * sizeof(float), true));
+    }
+    struct Step { int kind, size, symm, arg; };
+    std::vector<Step> seq;
+    unsigned x = seed * 2654435761u + 12345u;
+    auto rnd = [&](int m) { x = x * 1664525u + 1013904223u; return static_cast<int>((x >> 10) % m); };
+    for (int i = 0; i < length; ++i) seq.push_back(Step{rnd(9), rnd(4), rnd(2), rnd(64)});
+    w.run([&](int r, dlbb_comm* c) {
+        int rep = 0;
+        for (const Step& st : seq) {
+            ++rep;
+            const int64_t n = sizes[st.size];
+            Slot& sl = st.symm ? *symm[st.size] : *plain[st.size];
+            float* a = sl.a.at<float>(r);
+            float* b = sl.b.at<float>(r);
+            const int root = st.arg % P;
+            switch (st.kind) {
+                case 0: {   // all-reduce, in place, algorithm by argument
+                    const int algos[] = {DLBB_ALGO_AUTO, DLBB_ALGO_ONESHOT, DLBB_ALGO_TWOSHOT, DLBB_ALGO_NVLS};
+                    fill(a, r, n, rep);
+                    CALL(dlbb_allreduce(c, a, a, n, DLBB_F32, DLBB_SUM, algos[st.arg % 4], nullptr, nullptr));
+                    for (int64_t i = 0; i < n; ++i)
+                        if (to_d(a[i]) != reduce_expected(P, i, rep, DLBB_SUM)) { FAIL("mixed allreduce rank %d step %d elem %lld", r, rep, (long long)i); break; }
+                    break;
+                }
+                case 1: {   // all-reduce out of place
+                    fill(a, r, n, rep);
+                    CALL(dlbb_allreduce(c, a, b, n, DLBB_F32, DLBB_MAX, DLBB_ALGO_AUTO, nullptr, nullptr));
+                    for (int64_t i = 0; i < n; ++i)
+                        if (to_d(b[i]) != reduce_expected(P, i, rep, DLBB_MAX)) { FAIL("mixed allreduce(max) rank %d step %d elem %lld", r, rep, (long long)i); break; }
+                    break;
+                }
+                case 2: {
+                    if (r == root) mfill(a, root, n, rep);
+                    CALL(dlbb_broadcast(c, a, n, DLBB_F32, root, nullptr));
+                    expect_eq(a, n, root, rep, 0, r, "mixed broadcast");
+                    break;
+                }
+                case 3: {
+                    fill(a, r, n, rep);
+                    CALL(dlbb_reduce(c, a, a, n, DLBB_F32, DLBB_SUM, root, nullptr));
+                    if (r == root)
+                        for (int64_t i = 0; i < n; ++i)
+                            if (to_d(a[i]) != reduce_expected(P, i, rep, DLBB_SUM)) { FAIL("mixed reduce step %d elem %lld", rep, (long long)i); break; }
+                    break;
+                }
+                case 4: {
+                    mfill(a, r, n, rep);
+                    CALL(dlbb_allgather(c, a, b, n, DLBB_F32, nullptr, nullptr));
+                    for (int p = 0; p < P; ++p)
+                        if (!expect_eq(b + p * n, n, p, rep, 0, r, "mixed allgather")) break;
+                    break;
+                }
+                case 5: {
+                    const int64_t cpr = (n + 3) / 4 * 4;   // (buffers hold n * P floats; keep shards 16-byte multiples half of the time)
+                    const int64_t k = (st.arg & 1) ? cpr : n;
+                    if (k * P > n * P + 0 && k != n) { /* cpr * P may exceed the slot: fall back to n */ }
+                    const int64_t use = (k * P <= n * P) ? k : n;
+                    fill(a, r, use * P, rep);
+                    CALL(dlbb_reduce_scatter(c, a, b, use, DLBB_F32, DLBB_SUM, nullptr));
+                    for (int64_t i = 0; i < use; ++i)
+                        if (to_d(b[i]) != reduce_expected(P, r * use + i, rep, DLBB_SUM)) { FAIL("mixed reduce_scatter rank %d step %d elem %lld", r, rep, (long long)i); break; }
+                    break;
+                }
+                case 6: {
+                    mfill(a, r, n * P, rep);
+                    CALL(dlbb_alltoall(c, a, b, n, DLBB_F32, nullptr));
+                    for (int p = 0; p < P; ++p)
+                        if (!expect_eq(b + p * n, n, p, rep, r * n, r, "mixed alltoall")) break;
+                    break;
+                }
+                case 7: {
+                    mfill(a, r, n, rep);
+                    CALL(dlbb_gather(c, a, b, n, DLBB_F32, root, nullptr));
+                    if (r == root)
+                        for (int p = 0; p < P; ++p)
+                            if (!expect_eq(b + p * n, n, p, rep, 0, r, "mixed gather")) break;
+                    break;
+                }
+                default: {
+                    if (P > 2) {
+                        mfill(a, r, n, rep);
+                        CALL(dlbb_sendrecv(c, a, n, (r + 1) % P, b, n, (r + P - 1) % P, DLBB_F32, nullptr));
+                        expect_eq(b, n, (r + P - 1) % P, rep, 0, r, "mixed sendrecv");
+                    } else {
+                        CALL(dlbb_barrier(c, nullptr));
+                    }
+                    break;
+                }
+            }
+            g_checks.fetch_add(1);
+        }
+    });
+}
+
 // ------------------------------------------------------------------ driver
 static bool want(const char* filter, const char* group) { return filter == nullptr || strstr(group, filter) != nullptr; }
 
@@ -571,6 +750,14 @@ int main(int argc, char** argv) {
     if (want(filter, "ptrs"))
         for (int64_t n : {5, 1024, 20000})
             for (int root : {-1, 0, P - 1}) case_ptrs<float>(w, n, root);
+    if (want(filter, "fused_adam"))
+        for (int64_t n : {8, 1000, 4096 + 24, 30001}) {
+            case_fused_adam(w, n, 0, false, true);
+            case_fused_adam(w, n, 64, mc && P > 1, true);
+            case_fused_adam(w, n, 8, false, false);
+        }
+    if (want(filter, "mixed"))
+        for (unsigned seed = 1; seed <= (getenv("EMU_MIXED_SEEDS") ? (unsigned)atoi(getenv("EMU_MIXED_SEEDS")) : 6u); ++seed) case_mixed(w, seed, 60);
     if (want(filter, "views")) {
         case_views<float>(w, 2, 5, 16, false);
         case_views<__nv_bfloat16>(w, 3, 7, 24, false);
@@ -581,6 +768,9 @@ int main(int argc, char** argv) {
         printf("EMU COLLECTIVES FAILED: %d failures (world %d, %s)\n", g_fail.load(), P, mc ? "multicast" : "no multicast");
         return 1;
     }
+    printf("kernels:");
+    for (const auto& kv : emu::kernel_counts().n) printf(" %s=%ld", kv.first.c_str(), kv.second);
+    printf("\n");
     printf("EMU COLLECTIVES OK: world %d, %s, %ld checks, %ld kernel launches emulated\n", P, mc ? "multicast" : "no multicast",
            g_checks.load(), emu::launches().load());
     return 0;

@@ -1,0 +1,115 @@
+"""The collective kernels and their launchers (csrc/collectives/collectives.cu, direct_kernels.cuh) compiled for the host
+and run without a GPU (csrc/collectives/emu/, tools/emu_build.py): every rank and every CUDA thread is a host thread, the
+system-scope flags are release / acquire atomics, multicast windows are emulated.  Every collective entry point x dtype x
+reduce op x size x strided view is checked against plain arithmetic at world sizes 2-8 (3, 5, 6, 7 exist on no box), each
+call repeated back to back with the inputs rewritten in between, with thresholds lowered so that the large-message
+kernels (pipelined all-reduce, chain, two-hop relay / pull, zero-copy direct) run on kilobytes.  One build runs under
+ThreadSanitizer: a data access that the flag protocol does not order is reported as a race (SURVEY.md 5.2, section 4
+"world_size in {1,2,4,8}, every op x dtype x reduce-op x size").  A negative control with weakened flags proves the
+detector sees the protocol."""
+import os
+import re
+import subprocess
+import sys
+from pathlib import Path
+
+import pytest
+
+ROOT = Path(__file__).resolve().parent.parent
+
+
+def _build(tmp_path_factory, name, *extra):
+    out = tmp_path_factory.mktemp("emu") / name
+    r = subprocess.run([sys.executable, str(ROOT / "tools" / "emu_build.py"), "--out", str(out), *extra], capture_output=True,
+                       text=True, timeout=1200)
+    assert r.returncode == 0, r.stderr[-3000:]
+    return out
+
+
+@pytest.fixture(scope="module")
+def emu_plain(tmp_path_factory):
+    return _build(tmp_path_factory, "emu_collectives")
+
+
+@pytest.fixture(scope="module")
+def emu_tsan(tmp_path_factory):
+    probe = subprocess.run(["g++", "-fsanitize=thread", "-x", "c++", "-", "-o", "/dev/null"], input="int main(){}", text=True,
+                           capture_output=True)
+    if probe.returncode != 0:
+        pytest.skip("ThreadSanitizer runtime not available")
+    return _build(tmp_path_factory, "emu_collectives_tsan", "--sanitize", "thread")
+
+
+def _run(exe, world, mc, flt=None, env=None, timeout=1500):
+    e = dict(os.environ)
+    e.update(env or {})
+    cmd = [str(exe), str(world), "mc" if mc else "nomc"] + ([flt] if flt else [])
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=timeout, env=e)
+    out = r.stdout + r.stderr
+    assert r.returncode == 0 and "EMU COLLECTIVES OK" in out, out[-3000:]
+    m = re.search(r"^kernels:(.*)$", out, re.M)
+    kernels = dict((k, int(v)) for k, v in re.findall(r"(\S.*?)=(\d+)(?: |$)", m.group(1))) if m else {}
+    return out, kernels
+
+
+def _ran(kernels, prefix):
+    return sum(n for k, n in kernels.items() if k.startswith(prefix))
+
+
+@pytest.mark.parametrize("world,mc", [(2, True), (3, True), (5, False), (6, True), (7, False), (8, True)])   # (4: below, twice)
+def test_every_collective_at_every_world_size(emu_plain, world, mc):
+    out, k = _run(emu_plain, world, mc, env={"EMU_REPS": "2", "EMU_MIXED_SEEDS": "2"})
+    assert _ran(k, "fused_reduce_adam_kernel"), k
+    assert _ran(k, "reduce_kernel") and _ran(k, "move_kernel") and _ran(k, "p2p_kernel") and _ran(k, "reduce_multi_kernel"), k
+    assert _ran(k, "direct_reduce_kernel"), k                      # zero-copy in place
+    if world > 2:
+        assert _ran(k, "bcast_relay_kernel"), k
+    if mc and world > 2:
+        assert _ran(k, "allreduce_twoshot_kernel<T, OP, true>") and _ran(k, "broadcast_nvls_kernel"), k
+        assert _ran(k, "direct_reduce_kernel<T, OP, true, SINK_MC"), k   # multimem.ld_reduce + multimem.st in place
+
+
+@pytest.mark.parametrize("env,world,mc,flt,kernel", [
+    ({"DLBB_PIPELINE_MIN_BYTES": "32768", "EMU_CTAS": "2", "EMU_STAGE_KB": "256"}, 3, True, "allreduce", "allreduce_pipelined_kernel"),
+    ({"DLBB_CHAIN_MIN_BYTES": "16384"}, 4, True, "broadcast", "chain_broadcast_kernel"),
+    ({"DLBB_CHAIN_MIN_BYTES": "16384"}, 3, False, "reduce ", "chain_reduce_kernel"),
+    ({"DLBB_REDUCE_PULL": "1", "DLBB_REDUCE_PULL_MIN_BYTES": "8192", "DLBB_RELAY_CHUNK_KB": "1", "EMU_CTAS": "13"}, 7, True,
+     "reduce ", "reduce_pull_kernel"),
+    ({"DLBB_REDUCE_PULL": "1", "DLBB_REDUCE_PULL_MIN_BYTES": "8192", "DLBB_RELAY_CHUNK_KB": "1"}, 5, False, "reduce ", "reduce_pull_kernel"),
+    ({"DLBB_RELAY_CHUNK_KB": "1", "EMU_CTAS": "13", "DLBB_BCAST_MC_MAX_BYTES": "0"}, 7, True, "broadcast", "bcast_relay_kernel<false>"),
+    ({"DLBB_RELAY_CHUNK_KB": "1", "EMU_CTAS": "10"}, 6, False, "broadcast", "bcast_relay_kernel<false>"),
+    ({"DLBB_DIRECT_LEGACY": "1"}, 5, False, "allreduce", "allreduce_direct_kernel"),
+    ({"DLBB_MC_REDUCE_SCATTER": "1"}, 3, True, "reduce_scatter", "direct_reduce_kernel<T, OP, true, SINK_ONE"),
+    ({"DLBB_MC_WORLD2": "1"}, 2, True, "allreduce", "direct_reduce_kernel<T, OP, true, SINK_MC"),
+    ({"DLBB_FUSION": "0"}, 3, True, "multi", "reduce_kernel"),
+    ({"EMU_CTAS": "1", "EMU_STAGE_KB": "16", "EMU_ZC_MIN": "0", "EMU_REPS": "2"}, 4, True, None, "allreduce_twoshot_kernel"),   # everything staged, many slices
+    ({"DLBB_DEBUG_POISON": "1", "EMU_REPS": "2"}, 4, True, None, "reduce_kernel"),                          # 0xFF-filled staging
+])
+def test_threshold_selected_and_opt_in_kernels(emu_plain, env, world, mc, flt, kernel):
+    out, k = _run(emu_plain, world, mc, flt, env)
+    assert _ran(k, kernel), (kernel, k)
+
+
+@pytest.mark.parametrize("env,world,mc,flt", [
+    ({}, 3, True, "mixed"),            # different collectives back to back: what one kernel leaves behind, the next one meets
+    ({}, 4, True, "mixed"),
+    ({}, 4, False, "mixed"),
+    ({"EMU_REPS": "3"}, 3, True, "views"),
+    ({"EMU_REPS": "3"}, 3, False, "sendrecv"),
+    ({"EMU_REPS": "3"}, 3, True, "fused_adam"),
+    ({"EMU_REPS": "2", "DLBB_REDUCE_PULL": "1", "DLBB_REDUCE_PULL_MIN_BYTES": "8192", "DLBB_RELAY_CHUNK_KB": "1"}, 4, True, "reduce "),
+    ({"EMU_REPS": "2", "DLBB_RELAY_CHUNK_KB": "1", "EMU_CTAS": "6", "DLBB_BCAST_MC_MAX_BYTES": "0"}, 4, True, "broadcast"),
+    ({"DLBB_DEBUG_POISON": "1", "EMU_MIXED_SEEDS": "3"}, 3, False, "mixed"),   # the debug fill itself must not race with a slower reader
+    ({"EMU_REPS": "2", "DLBB_PIPELINE_MIN_BYTES": "32768", "EMU_CTAS": "1", "EMU_STAGE_KB": "256"}, 2, True, "allreduce"),
+])
+def test_flag_protocols_are_race_free_under_thread_sanitizer(emu_tsan, env, world, mc, flt):
+    out, _ = _run(emu_tsan, world, mc, flt, env, timeout=3000)
+    assert "ThreadSanitizer" not in out, out[-4000:]
+
+
+def test_thread_sanitizer_sees_the_protocol(tmp_path_factory, emu_tsan):
+    """Negative control: with the flags demoted to relaxed atomics the same run must report data races."""
+    weak = _build(tmp_path_factory, "emu_collectives_weak", "--sanitize", "thread", "--define", "EMU_WEAK_FLAGS")
+    r = subprocess.run([str(weak), "2", "mc", "allreduce"], capture_output=True, text=True, timeout=1500,
+                       env=dict(os.environ, EMU_REPS="2"))
+    assert "WARNING: ThreadSanitizer: data race" in r.stderr

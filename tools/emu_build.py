@@ -14,7 +14,7 @@ from pathlib import Path
 ROOT = Path(__file__).resolve().parent.parent
 COLL = ROOT / "csrc" / "collectives"
 # translation units of the emulation build (everything else is included from them)
-UNITS = ["collectives.cu"]
+UNITS = ["collectives.cu", "fused_adam.cu"]
 INCLUDED = ["direct_kernels.cuh", "coll_device.cuh", "view_math.h", "direct_math.h"]
 
 LAUNCH = re.compile(r"([A-Za-z_]\w*(?:\s*<[^<>;(){}]*>)?)\s*<<<(.*?)>>>", re.S)
