@@ -994,19 +994,75 @@ struct MultiTable {
     int64_t off[kMultiMax];        // element offset of the slot inside the staging region (16 B aligned)
 };
 
+// The table is walked as ONE index space of 16-byte staging vectors (slot t starts at vector off[t] * sizeof(T) / 16), so
+// the threads of the grid spread over all tensors at once - a bucket of many tiny tensors costs one round trip, not one
+// per tensor - and every thread has the loads from ALL peers of its vector in flight before it adds them up (in rank
+// order: every rank computes bit-identical sums).  A slot's last vector may be partly padding: it is moved whole inside
+// the staging area, and only its valid elements are read from / written to the tensor.
+template <typename T>
+__device__ __forceinline__ int multi_slot_of(const MultiTable& tb, int64_t g) {   // last slot that starts at or before vector g
+    int lo = 0, hi = tb.count - 1;
+    while (lo < hi) {
+        const int mid = (lo + hi + 1) >> 1;
+        if (((tb.off[mid] * (int64_t)sizeof(T)) >> 4) <= g) lo = mid;
+        else hi = mid - 1;
+    }
+    return lo;
+}
+
 template <typename T, int OP>
 __global__ void __launch_bounds__(kCollThreads)
-reduce_multi_kernel(CommDev c, const __grid_constant__ MultiTable tb, int64_t stage_off, int bank, uint32_t epoch) {
+reduce_multi_kernel(CommDev c, const __grid_constant__ MultiTable tb, int64_t total_vecs, int64_t stage_off, int bank,
+                    uint32_t epoch) {
+    constexpr int VE = 16 / sizeof(T);
+    constexpr int kW = 8;   // peers whose loads are in flight together
+    using A = typename Acc<T>::type;
     const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const int64_t nth = (int64_t)gridDim.x * blockDim.x;
-    T* my_stage = reinterpret_cast<T*>(c.stage[c.rank] + stage_off);
-    const ViewDev dense{};
-    for (int t = 0; t < tb.count; ++t)
-        pack_typed<T>(my_stage + tb.off[t], static_cast<const T*>(tb.buf[t]), dense, 0, tb.n[t], tid, nth);
+    char* my_stage = c.stage[c.rank] + stage_off;
+    for (int64_t g = tid; g < total_vecs; g += nth) {
+        const int t = multi_slot_of<T>(tb, g);
+        const int64_t e0 = (g - ((tb.off[t] * (int64_t)sizeof(T)) >> 4)) * VE;   // first element of this vector in tensor t
+        const int64_t left = tb.n[t] - e0;                                        // its valid elements (>= 1)
+        const T* src = static_cast<const T*>(tb.buf[t]);
+        if (left >= VE && (reinterpret_cast<uintptr_t>(src) & 15) == 0) {
+            st_v4(my_stage + (g << 4), ld_stream_v4(src + e0));
+        } else {
+            T* d = reinterpret_cast<T*>(my_stage + (g << 4));
+            for (int e = 0; e < VE && e < left; ++e) d[e] = src[e0 + e];
+        }
+    }
     grid_barrier(c, bank, gridDim.x, epoch);
-    for (int t = 0; t < tb.count; ++t)
-        reduce_range<T, OP>(c, c.stage, static_cast<T*>(tb.buf[t]), nullptr, stage_off + tb.off[t] * (int64_t)sizeof(T), tb.n[t],
-                            tid, nth);
+    for (int64_t g = tid; g < total_vecs; g += nth) {
+        const int t = multi_slot_of<T>(tb, g);
+        const int64_t e0 = (g - ((tb.off[t] * (int64_t)sizeof(T)) >> 4)) * VE;
+        const int64_t left = tb.n[t] - e0;
+        A acc[VE];
+        for (int p0 = 0; p0 < c.world; p0 += kW) {
+            uint4 buf[kW];
+#pragma unroll
+            for (int q = 0; q < kW; ++q)
+                if (p0 + q < c.world) buf[q] = ld_peer_v4(c.stage[p0 + q] + stage_off + (g << 4));
+#pragma unroll
+            for (int q = 0; q < kW; ++q) {
+                if (p0 + q < c.world) {
+                    const T* x = reinterpret_cast<const T*>(&buf[q]);
+#pragma unroll
+                    for (int e = 0; e < VE; ++e) acc[e] = (p0 + q == 0) ? to_acc<T>(x[e]) : red_op<OP, A>(acc[e], to_acc<T>(x[e]));
+                }
+            }
+        }
+        uint4 o;
+        T* ot = reinterpret_cast<T*>(&o);
+#pragma unroll
+        for (int e = 0; e < VE; ++e) ot[e] = from_acc<T>(acc[e]);
+        T* dst = static_cast<T*>(tb.buf[t]);
+        if (left >= VE && (reinterpret_cast<uintptr_t>(dst) & 15) == 0) {
+            st_v4(dst + e0, o);
+        } else {
+            for (int e = 0; e < VE && e < left; ++e) dst[e0 + e] = ot[e];
+        }
+    }
 }
 
 // ------------------------------------------------------------------------------------------
@@ -1433,10 +1489,13 @@ static int allreduce_impl(dlbb_comm* c, const void* in, void* out, const void* e
 
 template <typename T, int OP>
 static int launch_multi_T(dlbb_comm* c, const MultiTable& tb, int64_t bytes, cudaStream_t s) {
-    const int ctas = pick_ctas(c, bytes);
+    // latency-bound: about two staging vectors per thread, so that a bucket of small tensors is one round trip deep
+    const int64_t total_vecs = bytes >> 4;
+    const int ctas = c->ctas > 0 ? std::min(c->ctas, kMaxCtas)
+                                 : static_cast<int>(std::min<int64_t>(96, std::max<int64_t>(1, total_vecs / (2 * kCollThreads))));
     const int64_t so = next_stage_off(c, s);
     const uint32_t ep = ++c->epoch[0];
-    reduce_multi_kernel<T, OP><<<ctas, kCollThreads, 0, s>>>(c->dev, tb, so, 0, ep);
+    reduce_multi_kernel<T, OP><<<ctas, kCollThreads, 0, s>>>(c->dev, tb, total_vecs, so, 0, ep);
     DLBB_CHECK_LAUNCH("reduce_multi_kernel");
     return 0;
 }
