@@ -77,7 +77,7 @@ struct Bufs {
             emu::SymmSeg& s = w.alloc_symm((bytes + 255) / 256 * 256 + 256);
             for (int r = 0; r < w.P; ++r) p[r] = s.base[r];
         } else {
-            for (int r = 0; r < w.P; ++r) p[r] = emu::alloc_zero(bytes + 256);
+            for (int r = 0; r < w.P; ++r) p[r] = emu::alloc_zero(bytes);   // exact: AddressSanitizer sees a one-byte overrun
         }
     }
     template <typename T> T* at(int r, int64_t elem_off = 0) const { return reinterpret_cast<T*>(p[r]) + elem_off; }
@@ -321,7 +321,7 @@ static void case_multi(World& w, int tensors, int64_t n_each, int op) {
     std::vector<int64_t> counts;
     for (int t = 0; t < tensors; ++t) {
         counts.push_back(n_each + (t % 3) * 5 + (t == 1 ? 0 : t));   // ragged sizes, some not a multiple of 16 bytes
-        bufs.emplace_back(w, counts.back() * sizeof(T), false);
+        bufs.emplace_back(w, (counts.back() + 1) * sizeof(T), false);   // (+1: every third tensor starts one element in)
     }
     w.run([&](int r, dlbb_comm* c) {
         for (int rep = 0; rep < kReps; ++rep) {

@@ -107,6 +107,18 @@ def test_flag_protocols_are_race_free_under_thread_sanitizer(emu_tsan, env, worl
     assert "ThreadSanitizer" not in out, out[-4000:]
 
 
+def test_no_out_of_bounds_access_under_address_sanitizer(tmp_path_factory):
+    """Tensors are allocated to the byte: a kernel that rounds a tail up to a whole vector, or view arithmetic that leaves the
+    tensor, is an AddressSanitizer report."""
+    probe = subprocess.run(["g++", "-fsanitize=address", "-x", "c++", "-", "-o", "/dev/null"], input="int main(){}", text=True,
+                           capture_output=True)
+    if probe.returncode != 0:
+        pytest.skip("AddressSanitizer runtime not available")
+    exe = _build(tmp_path_factory, "emu_collectives_asan", "--sanitize", "address")
+    out, _ = _run(exe, 3, True, env={"EMU_REPS": "2", "EMU_MIXED_SEEDS": "2", "ASAN_OPTIONS": "detect_leaks=0"})
+    assert "AddressSanitizer" not in out, out[-4000:]
+
+
 def test_thread_sanitizer_sees_the_protocol(tmp_path_factory, emu_tsan):
     """Negative control: with the flags demoted to relaxed atomics the same run must report data races."""
     weak = _build(tmp_path_factory, "emu_collectives_weak", "--sanitize", "thread", "--define", "EMU_WEAK_FLAGS")
