@@ -358,6 +358,36 @@ __device__ __forceinline__ void reduce_batch(const CommDev& c, int64_t base_byte
     reduce_batch<T, OP>(c, c.stage, base_byte_off, i0, stride, nvec, out);
 }
 
+// One vector, the loads from ALL peers in flight before the first one is consumed (reduce_batch keeps kU vectors of ONE
+// peer in flight and walks the peers one after the other: right for bandwidth, but a message of at most one vector per
+// thread then pays `world` NVLink round trips in a row).  Summed in rank order like reduce_batch: bit-identical results.
+template <typename T, int OP>
+__device__ __forceinline__ uint4 reduce_wide(const CommDev& c, char* const (&bases)[DLBB_MAX_RANKS], int64_t base_byte_off, int64_t i) {
+    constexpr int VE = 16 / sizeof(T);
+    constexpr int kW = 8;
+    using A = typename Acc<T>::type;
+    A acc[VE];
+    for (int p0 = 0; p0 < c.world; p0 += kW) {
+        uint4 buf[kW];
+#pragma unroll
+        for (int q = 0; q < kW; ++q)
+            if (p0 + q < c.world) buf[q] = ld_peer_v4(bases[p0 + q] + base_byte_off + (i << 4));
+#pragma unroll
+        for (int q = 0; q < kW; ++q) {
+            if (p0 + q < c.world) {
+                const T* x = reinterpret_cast<const T*>(&buf[q]);
+#pragma unroll
+                for (int e = 0; e < VE; ++e) acc[e] = (p0 + q == 0) ? to_acc<T>(x[e]) : red_op<OP, A>(acc[e], to_acc<T>(x[e]));
+            }
+        }
+    }
+    uint4 o;
+    T* ot = reinterpret_cast<T*>(&o);
+#pragma unroll
+    for (int e = 0; e < VE; ++e) ot[e] = from_acc<T>(acc[e]);
+    return o;
+}
+
 template <typename T, int OP>
 __device__ __forceinline__ typename Acc<T>::type reduce_scalar(const CommDev& c, char* const (&bases)[DLBB_MAX_RANKS],
                                                                int64_t byte_off) {
@@ -399,6 +429,9 @@ __device__ __forceinline__ void reduce_range(const CommDev& c, char* const (&bas
     int64_t done = 0;
     if (vec_ok) {
         const int64_t nvec = red_n / VE;
+        if (nvec <= nth && extra == nullptr) {   // at most one vector per thread: latency-bound, all peers at once
+            if (tid < nvec) st_v4(reinterpret_cast<uint4*>(dst) + tid, reduce_wide<T, OP>(c, bases, base_b, tid));
+        } else
         for (int64_t i0 = tid; i0 < nvec; i0 += nth * kU) {
             uint4 o[kU];
             reduce_batch<T, OP>(c, bases, base_b, i0, nth, nvec, o);
@@ -1015,8 +1048,6 @@ __global__ void __launch_bounds__(kCollThreads)
 reduce_multi_kernel(CommDev c, const __grid_constant__ MultiTable tb, int64_t total_vecs, int64_t stage_off, int bank,
                     uint32_t epoch) {
     constexpr int VE = 16 / sizeof(T);
-    constexpr int kW = 8;   // peers whose loads are in flight together
-    using A = typename Acc<T>::type;
     const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const int64_t nth = (int64_t)gridDim.x * blockDim.x;
     char* my_stage = c.stage[c.rank] + stage_off;
@@ -1037,25 +1068,8 @@ reduce_multi_kernel(CommDev c, const __grid_constant__ MultiTable tb, int64_t to
         const int t = multi_slot_of<T>(tb, g);
         const int64_t e0 = (g - ((tb.off[t] * (int64_t)sizeof(T)) >> 4)) * VE;
         const int64_t left = tb.n[t] - e0;
-        A acc[VE];
-        for (int p0 = 0; p0 < c.world; p0 += kW) {
-            uint4 buf[kW];
-#pragma unroll
-            for (int q = 0; q < kW; ++q)
-                if (p0 + q < c.world) buf[q] = ld_peer_v4(c.stage[p0 + q] + stage_off + (g << 4));
-#pragma unroll
-            for (int q = 0; q < kW; ++q) {
-                if (p0 + q < c.world) {
-                    const T* x = reinterpret_cast<const T*>(&buf[q]);
-#pragma unroll
-                    for (int e = 0; e < VE; ++e) acc[e] = (p0 + q == 0) ? to_acc<T>(x[e]) : red_op<OP, A>(acc[e], to_acc<T>(x[e]));
-                }
-            }
-        }
-        uint4 o;
-        T* ot = reinterpret_cast<T*>(&o);
-#pragma unroll
-        for (int e = 0; e < VE; ++e) ot[e] = from_acc<T>(acc[e]);
+        const uint4 o = reduce_wide<T, OP>(c, c.stage, stage_off, g);
+        const T* ot = reinterpret_cast<const T*>(&o);
         T* dst = static_cast<T*>(tb.buf[t]);
         if (left >= VE && (reinterpret_cast<uintptr_t>(dst) & 15) == 0) {
             st_v4(dst + e0, o);
