@@ -64,6 +64,17 @@ struct World {
             }
             c->dev.stage_mc = mc ? stage.mc : nullptr;
             c->dev.pads_mc = mc ? reinterpret_cast<uint32_t*>(pads.mc) : nullptr;
+            // EMU_EPOCH0: start every epoch counter (and every flag) just below 2^32, so that the run crosses the wrap-around
+            if (const char* e0 = getenv("EMU_EPOCH0")) {
+                const uint32_t v = static_cast<uint32_t>(strtoul(e0, nullptr, 0));
+                for (uint32_t& e : c->epoch) e = v;
+                for (int p = 0; p < P; ++p) { c->send_epoch[p] = v; c->recv_epoch[p] = v; }
+                if (r == 0)
+                    for (int p = 0; p < P; ++p) {
+                        uint32_t* w = reinterpret_cast<uint32_t*>(pads.base[p]);
+                        for (size_t i = 0; i < dlbb::kPadBytes / 4; ++i) w[i] = v;
+                    }
+            }
             const char* wd = getenv("DLBB_WATCHDOG_SECONDS");
             c->dev.watchdog_ns = (wd ? atoll(wd) : 300) * 1000000000ll;
             comm.push_back(std::move(c));

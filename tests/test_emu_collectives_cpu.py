@@ -84,6 +84,7 @@ def test_every_collective_at_every_world_size(emu_plain, world, mc):
     ({"DLBB_FUSION": "0"}, 3, True, "multi", "reduce_kernel"),
     ({"EMU_CTAS": "1", "EMU_STAGE_KB": "16", "EMU_ZC_MIN": "0", "EMU_REPS": "2"}, 4, True, None, "allreduce_twoshot_kernel"),   # everything staged, many slices
     ({"DLBB_DEBUG_POISON": "1", "EMU_REPS": "2"}, 4, True, None, "reduce_kernel"),                          # 0xFF-filled staging
+    ({"EMU_EPOCH0": "0xFFFFFFC0", "EMU_REPS": "3"}, 3, True, None, "reduce_kernel"),                       # every epoch counter wraps past 2^32
 ])
 def test_threshold_selected_and_opt_in_kernels(emu_plain, env, world, mc, flt, kernel):
     out, k = _run(emu_plain, world, mc, flt, env)
@@ -99,6 +100,8 @@ def test_threshold_selected_and_opt_in_kernels(emu_plain, env, world, mc, flt, k
     ({"EMU_REPS": "3"}, 3, True, "fused_adam"),
     ({"EMU_REPS": "2", "DLBB_REDUCE_PULL": "1", "DLBB_REDUCE_PULL_MIN_BYTES": "8192", "DLBB_RELAY_CHUNK_KB": "1"}, 4, True, "reduce "),
     ({"EMU_REPS": "2", "DLBB_RELAY_CHUNK_KB": "1", "EMU_CTAS": "6", "DLBB_BCAST_MC_MAX_BYTES": "0"}, 4, True, "broadcast"),
+    # nothing zero-copy: the staged large-message kernels (pipelined, chain, multicast broadcast) share flag bank 4
+    ({"EMU_ZC_MIN": "0", "DLBB_PIPELINE_MIN_BYTES": "16384", "DLBB_CHAIN_MIN_BYTES": "16384", "EMU_CTAS": "2"}, 3, True, "mixed"),
     ({"DLBB_DEBUG_POISON": "1", "EMU_MIXED_SEEDS": "3"}, 3, False, "mixed"),   # the debug fill itself must not race with a slower reader
     ({"EMU_REPS": "2", "DLBB_PIPELINE_MIN_BYTES": "32768", "EMU_CTAS": "1", "EMU_STAGE_KB": "256"}, 2, True, "allreduce"),
 ])
