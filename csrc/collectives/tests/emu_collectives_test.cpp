@@ -680,6 +680,17 @@ int main(int argc, char** argv) {
     World w(P, stage, mc && P > 1, ctas, P > 1 ? zc_min : 0);
     emu::world() = &w;
 
+    if (filter && strcmp(filter, "watchdog") == 0) {
+        // the last rank never issues the collective: the others' flag waits must give up after DLBB_WATCHDOG_SECONDS and
+        // name it (the process aborts, as the GPU traps) - run on its own, expected to fail
+        g_case = "watchdog";
+        Bufs b(w, 4096, false);
+        w.run([&](int r, dlbb_comm* c) {
+            if (r != P - 1) dlbb_allreduce(c, b.at<float>(r), b.at<float>(r), 1024, DLBB_F32, DLBB_SUM, DLBB_ALGO_AUTO, nullptr, nullptr);
+        });
+        printf("watchdog did not fire\n");
+        return 3;
+    }
     const int64_t sizes[] = {1, 7, 300, 4099, 20000, 70001};
     if (want(filter, "allreduce")) {
         for (int64_t n : sizes) {

@@ -110,6 +110,14 @@ def test_flag_protocols_are_race_free_under_thread_sanitizer(emu_tsan, env, worl
     assert "ThreadSanitizer" not in out, out[-4000:]
 
 
+def test_device_watchdog_names_the_missing_rank(emu_plain):
+    """a rank that never arrives ends the others' flag waits after the deadline, with its number in the message."""
+    r = subprocess.run([str(emu_plain), "3", "nomc", "watchdog"], capture_output=True, text=True, timeout=120,
+                       env=dict(os.environ, DLBB_WATCHDOG_SECONDS="2"))
+    assert r.returncode != 0 and "watchdog did not fire" not in r.stdout
+    assert re.search(r"device barrier timeout: block \d+ waited 2000 ms for rank 2", r.stderr), r.stderr[-2000:]
+
+
 def test_no_out_of_bounds_access_under_address_sanitizer(tmp_path_factory):
     """Tensors are allocated to the byte: a kernel that rounds a tail up to a whole vector, or view arithmetic that leaves the
     tensor, is an AddressSanitizer report."""
