@@ -13,6 +13,11 @@
 //   * a launch runs its grid to completion on the calling thread's behalf (the rank's "stream" is the rank's host thread);
 //     ranks run independently, so kernel k+1 of one rank overlaps kernel k of another exactly as on the box
 //
+// What the emulation cannot see (these stay with the GPU tests): stale L1 lines (a cacheable load of data a peer wrote
+// during the kernel - ld_stream_v4 where ld_peer_v4 is needed - reads fresh data here), co-residency (all CTAs of a grid
+// run at once here; a grid barrier over more CTAs than fit on the device would only hang on the GPU), warp-level
+// primitives (none are used by these kernels), and of course time.
+//
 // tools/emu_build.py rewrites `kernel<<<grid, block, smem, stream>>>(args)` into EMU_LAUNCH(...) and compiles the
 // result; nothing else in the sources differs between the two builds.
 #ifndef DLBB_CUDA_EMU_H   // (reached both through -include and through relative includes: a guard, not #pragma once)
