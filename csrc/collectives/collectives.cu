@@ -1081,13 +1081,17 @@ reduce_multi_kernel(CommDev c, const __grid_constant__ MultiTable tb, int64_t to
 
 // ------------------------------------------------------------------------------------------
 // host side
+// Kernels with a GRID barrier (staged reduce_kernel / move_kernel, reduce_multi_kernel) need all their CTAs resident at
+// once: with 256 threads and up to ~190 registers that is one CTA per SM, so DLBB_CTAS above the SM count would leave CTAs
+// waiting for ones that can never start.  (Row-barrier kernels have no such limit: CTA b only meets CTA b of the peers.)
+constexpr int kMaxGridBarrierCtas = 128;
 static int pick_ctas(const dlbb_comm* c, int64_t bytes) {
     int n = c->ctas;
     if (n <= 0) {
         // one CTA per 128 KiB, capped: enough loads in flight to cover ~2 us of NVLink latency
         n = static_cast<int>(std::min<int64_t>(96, std::max<int64_t>(1, bytes / (64 << 10))));
     }
-    return std::min(n, kMaxCtas);
+    return std::min(n, kMaxGridBarrierCtas);
 }
 
 // Debug aid (DLBB_DEBUG_POISON=1): fill a staging region with 0xFF - NaN in every floating-point
@@ -1505,7 +1509,7 @@ template <typename T, int OP>
 static int launch_multi_T(dlbb_comm* c, const MultiTable& tb, int64_t bytes, cudaStream_t s) {
     // latency-bound: about two staging vectors per thread, so that a bucket of small tensors is one round trip deep
     const int64_t total_vecs = bytes >> 4;
-    const int ctas = c->ctas > 0 ? std::min(c->ctas, kMaxCtas)
+    const int ctas = c->ctas > 0 ? std::min(c->ctas, kMaxGridBarrierCtas)
                                  : static_cast<int>(std::min<int64_t>(96, std::max<int64_t>(1, total_vecs / (2 * kCollThreads))));
     const int64_t so = next_stage_off(c, s);
     const uint32_t ep = ++c->epoch[0];
