@@ -18,6 +18,7 @@
 
 #include "../../../include/dlbb.h"
 #include "../emu/emu_world.h"
+#include "../gemm_allreduce_fusion.cuh"
 
 using emu::World;
 
@@ -558,6 +559,82 @@ static void case_fused_adam(World& w, int64_t n, int64_t elem_off, bool use_mc, 
     });
 }
 
+// ------------------------------------------------------------------ K16: the all-reduce half of the fused GEMM + all-reduce
+// The tensor-core half cannot run here; a stand-in producer plays the GEMM roles of gemm_cta_body: CTA b "computes" tiles
+// b, b + grid, ... of the persistent schedule by writing rank- and element-dependent values into this rank's partial
+// buffer, and its leader calls ArFusion::tile_stored for each; threads >= kNumThreads are the real reducer warps
+// (ArFusion::extra_role), and everybody ends in ArFusion::finish - the functor is the one gemm_allreduce.cu compiles.
+static inline double pval(int rank, int64_t e, int rep) { return static_cast<double>(((e * 5 + rank * 7 + rep * 3) % 7) - 3); }
+
+static void emu_gemm_allreduce_kernel(dlbb::ArFusion f, __nv_bfloat16* my_part, int rep) {
+    using namespace dlbb;
+    if (threadIdx.x < (unsigned)kNumThreads) {
+        for (int t = blockIdx.x; t < f.num_tiles; t += gridDim.x) {
+            int m_blk, n_blk;
+            tile_coords(t, f.num_m, f.num_n, f.group_m, m_blk, n_blk);
+            const int m0 = m_blk * kBM, n0 = n_blk * f.bn;
+            const int rows = std::min(kBM, f.M - m0), cols = std::min(f.bn, f.N - n0);
+            for (int i = threadIdx.x; i < rows * cols; i += kNumThreads) {
+                const int64_t e = (int64_t)(m0 + i / cols) * f.N + n0 + i % cols;
+                my_part[e] = __float2bfloat16(static_cast<float>(pval(f.c.rank, e, rep)));
+            }
+            group_bar_sync(1, kNumThreads);          // the whole tile is written ...
+            if (threadIdx.x == 0) f.tile_stored(t, m0, n0);   // ... before the leader raises its flag
+        }
+    } else {
+        f.extra_role(0, 0);
+    }
+    f.finish();
+}
+
+static void case_gemm_allreduce(World& w, int M, int N, int group_m, int grid, bool use_mc, bool with_residual) {
+    char name[160];
+    snprintf(name, sizeof(name), "gemm_allreduce M=%d N=%d group_m=%d grid=%d %s %s", M, N, group_m, grid, use_mc ? "multimem" : "peer",
+             with_residual ? "residual" : "noresidual");
+    g_case = name;
+    using T = __nv_bfloat16;
+    using namespace dlbb;
+    const int P = w.P, BN = 256;
+    const size_t bytes = ((size_t)M * N * sizeof(T) + 255) / 256 * 256;
+    w.alloc_symm(bytes);
+    const int part_seg = static_cast<int>(w.segs.size()) - 1;
+    w.alloc_symm(bytes);
+    const int out_seg = static_cast<int>(w.segs.size()) - 1;
+    Bufs res(w, (size_t)M * N * sizeof(T), false);
+    const int num_m = (M + kBM - 1) / kBM, num_n = (N + BN - 1) / BN;
+    grid = std::min(grid, std::max(2, 24 / P));   // 512 host threads per CTA and rank: stay below the process's thread limit
+    w.run([&](int r, dlbb_comm* c) {
+        T* rs = res.at<T>(r);
+        const T* out = reinterpret_cast<const T*>(w.segs[out_seg].base[r]);
+        for (int rep = 0; rep < kReps; ++rep) {
+            if (with_residual)
+                for (int64_t e = 0; e < (int64_t)M * N; ++e) rs[e] = from_d<T>(static_cast<double>((e + rep) % 3));
+            ArFusion f{};   // as dlbb_gemm_allreduce_bf16 fills it
+            f.c = c->dev;
+            for (int q = 0; q < P; ++q) {
+                f.part[q] = w.segs[part_seg].base[q];
+                f.out[q] = w.segs[out_seg].base[q];
+            }
+            const bool nvls = use_mc && w.segs[part_seg].mc && P > 1;
+            f.part_mc = nvls ? w.segs[part_seg].mc : nullptr;
+            f.out_mc = nvls ? w.segs[out_seg].mc : nullptr;
+            f.residual = with_residual ? rs : nullptr;
+            f.ld_res = N;
+            f.M = M; f.N = N; f.bn = BN; f.num_m = num_m; f.num_n = num_n; f.num_tiles = num_m * num_n; f.group_m = group_m;
+            f.epoch = ++c->epoch[kArBank];
+            EMU_LAUNCH(std::min(grid, num_m * num_n), kArThreads, emu_gemm_allreduce_kernel)(f, reinterpret_cast<T*>(w.segs[part_seg].base[r]), rep);
+            for (int64_t e = 0; e < (int64_t)M * N; ++e) {
+                double x = 0;
+                for (int q = 0; q < P; ++q) x += pval(q, e, rep);
+                if (with_residual) x += static_cast<double>((e + rep) % 3);
+                const double g = to_d(out[e]);
+                if (g != x) { FAIL("rank %d rep %d elem %lld: got %g expected %g", r, rep, (long long)e, g, x); break; }
+            }
+            g_checks.fetch_add(1);
+        }
+    });
+}
+
 // ------------------------------------------------------------------ mixed sequences
 // Different collectives back to back on one communicator, no host synchronisation in between: what one kernel leaves
 // behind in the staging halves / flag banks is what the next one starts from.  (Cases above join their rank threads
@@ -761,6 +838,12 @@ int main(int argc, char** argv) {
     if (want(filter, "ptrs"))
         for (int64_t n : {5, 1024, 20000})
             for (int root : {-1, 0, P - 1}) case_ptrs<float>(w, n, root);
+    if (want(filter, "gemm_allreduce")) {
+        case_gemm_allreduce(w, 256, 512, 2, 3, false, true);            // 2 x 2 tiles, more tiles than CTAs
+        case_gemm_allreduce(w, 200, 264, 1, 2, mc && P > 1, true);      // ragged last row / column of tiles
+        case_gemm_allreduce(w, 640, 256, 5, 4, mc && P > 1, false);     // one column of five tiles in one group
+        case_gemm_allreduce(w, 384, 768, 2, 9, false, false);           // as many CTAs as tiles, group of 2 + a group of 1
+    }
     if (want(filter, "fused_adam"))
         for (int64_t n : {8, 1000, 4096 + 24, 30001}) {
             case_fused_adam(w, n, 0, false, true);

@@ -12,15 +12,14 @@
 
 #include "../../include/dlbb.h"
 #include "common.cuh"
+#include "gemm_tiles.h"
 #include "ptx.cuh"
 
 namespace dlbb {
 
-constexpr int kBM = 128;
 constexpr int kBK = 64;          // 64 bf16 = 128 bytes = one swizzle row
 constexpr int kEpiCols = 32;     // epilogue chunk width (64 B rows, 64B swizzle)
 constexpr int kEpiBufBytes = kBM * kEpiCols * 2;  // 8 KiB
-constexpr int kNumThreads = 256;
 constexpr int kEpiThreads = 128;
 
 // CG = CTAs per MMA (1, or 2 = a CTA pair sharing one 256 x BN tile; each CTA then stages only half of B).
@@ -45,17 +44,6 @@ struct GemmParams {
     int group_m;   // tile rasterisation: m-blocks per group
     uint64_t a_policy, b_policy;  // L2 eviction priority of the operand panels
 };
-
-__device__ __forceinline__ void tile_coords(int t, int num_m, int num_n, int group_m, int& m_blk,
-                                            int& n_blk) {
-    const int per_group = group_m * num_n;
-    const int g = t / per_group;
-    const int first_m = g * group_m;
-    const int gsize = min(group_m, num_m - first_m);
-    const int r = t - g * per_group;
-    m_blk = first_m + r % gsize;
-    n_blk = r / gsize;
-}
 
 // Hook points for kernels that fuse more work into the GEMM (see csrc/collectives/gemm_allreduce.cu):
 //   tile_stored(t, m0, n0)  epilogue leader thread, after the last TMA store of tile t was committed

@@ -1,5 +1,5 @@
 """The collective kernels and their launchers (csrc/collectives/collectives.cu, direct_kernels.cuh) compiled for the host
-and run without a GPU (csrc/collectives/emu/, tools/emu_build.py): every rank and every CUDA thread is a host thread, the
+- plus fused_adam.cu and the functor of the fused GEMM + all-reduce - and run without a GPU (csrc/collectives/emu/, tools/emu_build.py): every rank and every CUDA thread is a host thread, the
 system-scope flags are release / acquire atomics, multicast windows are emulated.  Every collective entry point x dtype x
 reduce op x size x strided view is checked against plain arithmetic at world sizes 2-8 (3, 5, 6, 7 exist on no box), each
 call repeated back to back with the inputs rewritten in between, with thresholds lowered so that the large-message
@@ -59,7 +59,7 @@ def _ran(kernels, prefix):
 @pytest.mark.parametrize("world,mc", [(2, True), (3, True), (5, False), (6, True), (7, False), (8, True)])   # (4: below, twice)
 def test_every_collective_at_every_world_size(emu_plain, world, mc):
     out, k = _run(emu_plain, world, mc, env={"EMU_REPS": "2", "EMU_MIXED_SEEDS": "2"})
-    assert _ran(k, "fused_reduce_adam_kernel"), k
+    assert _ran(k, "fused_reduce_adam_kernel") and _ran(k, "emu_gemm_allreduce_kernel"), k
     assert _ran(k, "reduce_kernel") and _ran(k, "move_kernel") and _ran(k, "p2p_kernel") and _ran(k, "reduce_multi_kernel"), k
     assert _ran(k, "direct_reduce_kernel"), k                      # zero-copy in place
     if world > 2:
@@ -98,6 +98,8 @@ def test_threshold_selected_and_opt_in_kernels(emu_plain, env, world, mc, flt, k
     ({"EMU_REPS": "3"}, 3, True, "views"),
     ({"EMU_REPS": "3"}, 3, False, "sendrecv"),
     ({"EMU_REPS": "3"}, 3, True, "fused_adam"),
+    ({"EMU_REPS": "3"}, 3, True, "gemm_allreduce"),     # reducer warps + per-tile flags of the fused GEMM + all-reduce
+    ({"EMU_REPS": "3"}, 4, False, "gemm_allreduce"),
     ({"EMU_REPS": "2", "DLBB_REDUCE_PULL": "1", "DLBB_REDUCE_PULL_MIN_BYTES": "8192", "DLBB_RELAY_CHUNK_KB": "1"}, 4, True, "reduce "),
     ({"EMU_REPS": "2", "DLBB_RELAY_CHUNK_KB": "1", "EMU_CTAS": "6", "DLBB_BCAST_MC_MAX_BYTES": "0"}, 4, True, "broadcast"),
     # nothing zero-copy: the staged large-message kernels (pipelined, chain, multicast broadcast) share flag bank 4

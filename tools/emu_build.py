@@ -15,7 +15,7 @@ ROOT = Path(__file__).resolve().parent.parent
 COLL = ROOT / "csrc" / "collectives"
 # translation units of the emulation build (everything else is included from them)
 UNITS = ["collectives.cu", "fused_adam.cu"]
-INCLUDED = ["direct_kernels.cuh", "coll_device.cuh", "view_math.h", "direct_math.h"]
+INCLUDED = ["direct_kernels.cuh", "coll_device.cuh", "view_math.h", "direct_math.h", "gemm_allreduce_fusion.cuh"]
 
 LAUNCH = re.compile(r"([A-Za-z_]\w*(?:\s*<[^<>;(){}]*>)?)\s*<<<(.*?)>>>", re.S)
 
