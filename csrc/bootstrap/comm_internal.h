@@ -79,6 +79,8 @@ struct dlbb_comm {
     uint32_t recv_epoch[DLBB_MAX_RANKS] = {};
     unsigned parity = 0;           // alternates the staging half used by single-barrier kernels
     int ctas = 0;                  // 0 = auto
+    int max_resident_ctas = 128;   // most CTAs a kernel with a GRID barrier may launch: they must all be resident together
+                                   // (min(128, SM count) unless DLBB_MAX_RESIDENT_CTAS says otherwise - SM-limited partitions)
     size_t oneshot_max = 0;        // 0 = auto
     int default_algo = 0;          // DLBB_ALGO: what DLBB_ALGO_AUTO resolves to (0 = size-based choice)
     dlbb::PeerRegistry* reg = nullptr;   // zero-copy access to the peers' ordinary allocations

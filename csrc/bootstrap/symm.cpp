@@ -354,6 +354,13 @@ int dlbb_comm_create(int rank, int world, int device, const char* job, size_t st
     fill_dev(c);
     const char* e = getenv("DLBB_CTAS");
     if (e) c->ctas = atoi(e);
+    {
+        int sms = 0;
+        if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device) == cudaSuccess && sms > 0)
+            c->max_resident_ctas = sms < 128 ? sms : 128;
+        e = getenv("DLBB_MAX_RESIDENT_CTAS");
+        if (e && atoi(e) > 0) c->max_resident_ctas = atoi(e);
+    }
     e = getenv("DLBB_ONESHOT_MAX_BYTES");
     if (e) c->oneshot_max = static_cast<size_t>(atol(e));
     e = getenv("DLBB_ALGO");   // analogue of CCL_ALLREDUCE (collectives/3d/launch_dsccl.sh:46)

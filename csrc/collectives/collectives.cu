@@ -431,8 +431,7 @@ __device__ __forceinline__ void reduce_range(const CommDev& c, char* const (&bas
         const int64_t nvec = red_n / VE;
         if (nvec <= nth && extra == nullptr) {   // at most one vector per thread: latency-bound, all peers at once
             if (tid < nvec) st_v4(reinterpret_cast<uint4*>(dst) + tid, reduce_wide<T, OP>(c, bases, base_b, tid));
-        } else
-        for (int64_t i0 = tid; i0 < nvec; i0 += nth * kU) {
+        } else for (int64_t i0 = tid; i0 < nvec; i0 += nth * kU) {
             uint4 o[kU];
             reduce_batch<T, OP>(c, bases, base_b, i0, nth, nvec, o);
 #pragma unroll
@@ -1083,15 +1082,16 @@ reduce_multi_kernel(CommDev c, const __grid_constant__ MultiTable tb, int64_t to
 // host side
 // Kernels with a GRID barrier (staged reduce_kernel / move_kernel, reduce_multi_kernel) need all their CTAs resident at
 // once: with 256 threads and up to ~190 registers that is one CTA per SM, so DLBB_CTAS above the SM count would leave CTAs
-// waiting for ones that can never start.  (Row-barrier kernels have no such limit: CTA b only meets CTA b of the peers.)
-constexpr int kMaxGridBarrierCtas = 128;
+// waiting for ones that can never start: they are clamped to dlbb_comm::max_resident_ctas.  (Row-barrier kernels have no
+// such limit: CTA b only meets CTA b of the peers and, in the two-hop kernels, lower-numbered CTAs - the host emulation
+// runs them with fewer CTA slots than CTAs to prove it.)
 static int pick_ctas(const dlbb_comm* c, int64_t bytes) {
     int n = c->ctas;
     if (n <= 0) {
         // one CTA per 128 KiB, capped: enough loads in flight to cover ~2 us of NVLink latency
         n = static_cast<int>(std::min<int64_t>(96, std::max<int64_t>(1, bytes / (64 << 10))));
     }
-    return std::min(n, kMaxGridBarrierCtas);
+    return std::min(n, c->max_resident_ctas);
 }
 
 // Debug aid (DLBB_DEBUG_POISON=1): fill a staging region with 0xFF - NaN in every floating-point
@@ -1509,8 +1509,8 @@ template <typename T, int OP>
 static int launch_multi_T(dlbb_comm* c, const MultiTable& tb, int64_t bytes, cudaStream_t s) {
     // latency-bound: about two staging vectors per thread, so that a bucket of small tensors is one round trip deep
     const int64_t total_vecs = bytes >> 4;
-    const int ctas = c->ctas > 0 ? std::min(c->ctas, kMaxGridBarrierCtas)
-                                 : static_cast<int>(std::min<int64_t>(96, std::max<int64_t>(1, total_vecs / (2 * kCollThreads))));
+    const int want = c->ctas > 0 ? c->ctas : static_cast<int>(std::min<int64_t>(96, std::max<int64_t>(1, total_vecs / (2 * kCollThreads))));
+    const int ctas = std::min(want, c->max_resident_ctas);   // grid barrier inside
     const int64_t so = next_stage_off(c, s);
     const uint32_t ep = ++c->epoch[0];
     reduce_multi_kernel<T, OP><<<ctas, kCollThreads, 0, s>>>(c->dev, tb, total_vecs, so, 0, ep);

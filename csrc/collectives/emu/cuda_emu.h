@@ -14,9 +14,8 @@
 //     ranks run independently, so kernel k+1 of one rank overlaps kernel k of another exactly as on the box
 //
 // What the emulation cannot see (these stay with the GPU tests): stale L1 lines (a cacheable load of data a peer wrote
-// during the kernel - ld_stream_v4 where ld_peer_v4 is needed - reads fresh data here), co-residency (all CTAs of a grid
-// run at once here; a grid barrier over more CTAs than fit on the device would only hang on the GPU), warp-level
-// primitives (none are used by these kernels), and of course time.
+// during the kernel - ld_stream_v4 where ld_peer_v4 is needed - reads fresh data here), warp-level primitives (none are
+// used by these kernels), and of course time.  Limited residency IS modelled (EMU_RESIDENT_CTAS, see run_grid).
 //
 // tools/emu_build.py rewrites `kernel<<<grid, block, smem, stream>>>(args)` into EMU_LAUNCH(...) and compiles the
 // result; nothing else in the sources differs between the two builds.
@@ -103,6 +102,14 @@ inline KernelCounts& kernel_counts() {
     return k;
 }
 
+// EMU_RESIDENT_CTAS = N: at most N CTAs of a grid run at a time, started in blockIdx order as slots free up - what the
+// hardware does when a grid does not fit.  A kernel in which a CTA waits for a higher-numbered CTA of its own grid, or a
+// grid barrier over more CTAs than slots, then stops making progress here too (and the watchdog reports it).
+inline int resident_ctas() {
+    static const int v = getenv("EMU_RESIDENT_CTAS") ? atoi(getenv("EMU_RESIDENT_CTAS")) : 0;
+    return v;
+}
+
 template <typename F>
 void run_grid(int grid, int block, F&& body) {
     if (block < keep_block_at()) block = std::min(block, max_block());
@@ -110,7 +117,17 @@ void run_grid(int grid, int block, F&& body) {
     std::vector<Cta> ctas(grid);
     std::vector<std::thread> th;
     th.reserve(static_cast<size_t>(grid) * block);
-    for (int b = 0; b < grid; ++b)
+    const int slots = resident_ctas() > 0 ? resident_ctas() : grid;
+    std::mutex m;
+    std::condition_variable cv;
+    int running = 0;
+    std::vector<int> left(grid, block);   // threads of CTA b still running (under m)
+    for (int b = 0; b < grid; ++b) {
+        {
+            std::unique_lock<std::mutex> lk(m);
+            cv.wait(lk, [&] { return running < slots; });
+            ++running;
+        }
         for (int t = 0; t < block; ++t)
             th.emplace_back([&, b, t] {
                 threadIdx = uint3{static_cast<unsigned>(t), 0, 0};
@@ -119,7 +136,13 @@ void run_grid(int grid, int block, F&& body) {
                 gridDim = dim3(grid);
                 tl_cta = &ctas[b];
                 body();
+                std::lock_guard<std::mutex> lk(m);
+                if (--left[b] == 0) {
+                    --running;
+                    cv.notify_all();
+                }
             });
+    }
     for (auto& x : th) x.join();
 }
 

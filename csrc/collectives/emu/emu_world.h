@@ -53,6 +53,10 @@ struct World {
             c->mc_supported = mc;
             c->stage_bytes = stage_bytes;
             c->ctas = ctas;
+            // the emulated device has EMU_RESIDENT_CTAS slots (cuda_emu.h); EMU_NO_CLAMP keeps the library unaware of it
+            // (negative control: a grid barrier over more CTAs than slots must then stall until the watchdog fires)
+            if (const char* e = getenv("EMU_RESIDENT_CTAS"))
+                if (!getenv("EMU_NO_CLAMP")) c->max_resident_ctas = atoi(e) > 0 ? atoi(e) : 128;
             c->zero_copy_min = zero_copy_min;
             c->debug_poison = getenv("DLBB_DEBUG_POISON") != nullptr && atoi(getenv("DLBB_DEBUG_POISON")) != 0;
             c->dev.rank = r;

@@ -84,6 +84,8 @@ def test_every_collective_at_every_world_size(emu_plain, world, mc):
     ({"DLBB_FUSION": "0"}, 3, True, "multi", "reduce_kernel"),
     ({"EMU_CTAS": "1", "EMU_STAGE_KB": "16", "EMU_ZC_MIN": "0", "EMU_REPS": "2"}, 4, True, None, "allreduce_twoshot_kernel"),   # everything staged, many slices
     ({"DLBB_DEBUG_POISON": "1", "EMU_REPS": "2"}, 4, True, None, "reduce_kernel"),                          # 0xFF-filled staging
+    # a device with 3 CTA slots and 7 CTAs asked for: grid-barrier kernels are clamped, the others run in waves
+    ({"EMU_CTAS": "7", "EMU_RESIDENT_CTAS": "3", "EMU_REPS": "2", "EMU_MIXED_SEEDS": "2"}, 4, True, None, "move_kernel"),
     ({"EMU_EPOCH0": "0xFFFFFFC0", "EMU_REPS": "3"}, 3, True, None, "reduce_kernel"),                       # every epoch counter wraps past 2^32
 ])
 def test_threshold_selected_and_opt_in_kernels(emu_plain, env, world, mc, flt, kernel):
@@ -118,6 +120,14 @@ def test_device_watchdog_names_the_missing_rank(emu_plain):
                        env=dict(os.environ, DLBB_WATCHDOG_SECONDS="2"))
     assert r.returncode != 0 and "watchdog did not fire" not in r.stdout
     assert re.search(r"device barrier timeout: block \d+ waited 2000 ms for rank 2", r.stderr), r.stderr[-2000:]
+
+
+def test_grid_barrier_over_more_ctas_than_fit_is_detected(emu_plain):
+    """Negative control for the residency model: with the library's clamp disabled, a grid-barrier kernel of 7 CTAs on a
+    device with 3 slots stalls (CTA 0 waits for CTAs that cannot start) and the watchdog fires."""
+    r = subprocess.run([str(emu_plain), "2", "nomc", "allgather"], capture_output=True, text=True, timeout=120,
+                       env=dict(os.environ, DLBB_WATCHDOG_SECONDS="2", EMU_NO_CLAMP="1", EMU_CTAS="7", EMU_RESIDENT_CTAS="3", EMU_REPS="1"))
+    assert r.returncode != 0 and "device barrier timeout" in r.stderr, r.stderr[-2000:]
 
 
 def test_no_out_of_bounds_access_under_address_sanitizer(tmp_path_factory):
