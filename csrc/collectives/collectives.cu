@@ -1211,7 +1211,9 @@ static int launch_twoshot_T(dlbb_comm* c, bool nvls, const void* src, void* dst,
         // (measured at 8 GPUs, 256 MiB: 631 GB/s busbw vs 515 for the phase-by-phase kernel and 646 for NCCL;
         // the peer-load variant does not profit - 362 vs 430 - and keeps the phase-by-phase kernel)
         constexpr int VE = 16 / sizeof(T);
-        const int ctas = c->ctas > 0 ? std::min(c->ctas, 148) : 128;   // one 512-thread CTA per SM: all rows must be resident
+        // one 512-thread CTA per SM, and a row's reduce role waits for the pack roles of ALL rows of the peers: every
+        // CTA must be resident
+        const int ctas = std::min(c->ctas > 0 ? c->ctas : 128, c->max_resident_ctas);
         const int64_t per = (n / VE + ctas - 1) / ctas;
         static const int kPipeChunkVecs = getenv("DLBB_PIPE_CHUNK_KB") ? atoi(getenv("DLBB_PIPE_CHUNK_KB")) * 64 : kPipeChunkVecsDefault;
         const uint32_t nchunks = static_cast<uint32_t>((per + kPipeChunkVecs - 1) / kPipeChunkVecs);

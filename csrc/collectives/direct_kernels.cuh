@@ -244,6 +244,71 @@ bcast_relay_kernel(CommDev c, const __grid_constant__ PeerView pv, int64_t nvec,
     row_barrier(c, bank, blockIdx.x, epoch + 1);
 }
 
+// ------------------------------------------------------------------------------------------
+// Broadcast relay, push form (opt-in: DLBB_BCAST_PUSH=1; verified on the host emulation, not yet measured on a box).
+// Same two hops and the same shares as the pull relay above, but every hop is a STORE: the root writes share j into relay
+// j's tensor chunk by chunk and raises "chunk k is there" on that relay's pad; relay j, one group of CTAs per destination,
+// waits for the flag, reads the chunk out of its OWN tensor (coherent loads: it was written during this kernel) and
+// writes it into the tensor of one of the other P-2 relays.  No read request crosses NVLink, the only flags go
+// root -> relay, and the closing row barrier tells every rank that all stores into its tensor have landed.
+// Grid: (P-1) groups x rows on every rank.  Root: group g pushes share g.  Relay: group g < P-2 serves its g-th other
+// relay, the last group has nothing to do (it only takes part in the barriers).
+__global__ void __launch_bounds__(kDirThreads)
+bcast_push_kernel(CommDev c, const __grid_constant__ PeerView pv, int64_t nvec, int root, int rows, uint32_t flag_base,
+                  int bank, uint32_t epoch, int chunk_vecs) {
+    const int P = c.world;
+    const bool is_root = c.rank == root;
+    const int me = relay_index(c.rank, root, P);
+    // CTAs are numbered row-major (the P-1 groups of a row are neighbours): a relay's CTA waits for the root's CTA of the
+    // same row, which is at most P-2 blocks away - with in-order block scheduling the kernel makes progress on any device
+    // that holds P-1 CTAs at a time, however many rows there are (group-major numbering stalled in the emulation with
+    // fewer slots than CTAs: the root's early CTAs sat in the closing barrier while its late ones could not start).
+    const int row = blockIdx.x / (P - 1), group = blockIdx.x - row * (P - 1);
+    const int nchunks = share_nchunks(nvec, P - 1, rows, chunk_vecs);
+    row_barrier(c, bank, blockIdx.x, epoch);
+    const int j = is_root ? group : me;                       // the share this CTA moves
+    int64_t s_lo, r_lo, r_hi;
+    share_row_range(nvec, P - 1, rows, j, row, s_lo, r_lo, r_hi);
+    char* mine = pv.ptr[c.rank];
+    if (is_root) {
+        const int relay = relay_rank(group, root, P);
+        char* to = pv.ptr[relay];
+        for (int k = 0; k < nchunks; ++k) {
+            int64_t c_lo, c_hi;
+            chunk_range(r_lo, r_hi, k, chunk_vecs, c_lo, c_hi);
+            for (int64_t i0 = c_lo + threadIdx.x; i0 < c_hi; i0 += (int64_t)blockDim.x * kU) {
+                uint4 v[kU];
+#pragma unroll
+                for (int u = 0; u < kU; ++u)
+                    if (i0 + u * blockDim.x < c_hi) v[u] = ld_stream_v4(mine + ((i0 + u * blockDim.x) << 4));
+#pragma unroll
+                for (int u = 0; u < kU; ++u)
+                    if (i0 + u * blockDim.x < c_hi) st_v4(to + ((i0 + u * blockDim.x) << 4), v[u]);
+            }
+            __syncthreads();   // the whole chunk has been issued by this CTA; the release below orders it for the relay
+            if (threadIdx.x == 0) st_release_sys(pad_slot(c, relay, kRelayBank, row, root), flag_base + k + 1);
+        }
+    } else if (group < P - 2) {
+        char* to = pv.ptr[relay_rank(other_relay(me, group + 1, P), root, P)];
+        for (int k = 0; k < nchunks; ++k) {
+            int64_t c_lo, c_hi;
+            chunk_range(r_lo, r_hi, k, chunk_vecs, c_lo, c_hi);
+            if (threadIdx.x == 0) wait_flag(pad_slot(c, c.rank, kRelayBank, row, root), flag_base + k + 1, root, c.watchdog_ns);
+            __syncthreads();
+            for (int64_t i0 = c_lo + threadIdx.x; i0 < c_hi; i0 += (int64_t)blockDim.x * kU) {
+                uint4 v[kU];
+#pragma unroll
+                for (int u = 0; u < kU; ++u)
+                    if (i0 + u * blockDim.x < c_hi) v[u] = ld_peer_v4(mine + ((i0 + u * blockDim.x) << 4));
+#pragma unroll
+                for (int u = 0; u < kU; ++u)
+                    if (i0 + u * blockDim.x < c_hi) st_v4(to + ((i0 + u * blockDim.x) << 4), v[u]);
+            }
+        }
+    }
+    row_barrier(c, bank, blockIdx.x, epoch + 1);
+}
+
 // ------------------------------------------------------------------------------------------ host side
 // DLBB_MC_* / DLBB_BCAST_MC: 1 = use the multimem form whenever the buffers have a multicast mapping
 // (the default), 0 = plain peer loads / stores even then (for the tuning study).
@@ -394,6 +459,11 @@ static int launch_bcast_relay(dlbb_comm* c, const PeerView& pv, int64_t nvec, in
     if (!mc) c->epoch[kRelayBank] += nchunks;
     const uint32_t ep = c->epoch[0] + 1;
     c->epoch[0] += 2;
+    if (!mc && env_flag("DLBB_BCAST_PUSH", false)) {   // same shares, rows, chunks and flag epochs; stores instead of loads
+        bcast_push_kernel<<<ctas, kDirThreads, 0, s>>>(c->dev, pv, nvec, root, rows, fb, 0, ep, kRelayChunkVecs);
+        DLBB_CHECK_LAUNCH("bcast_push_kernel");
+        return 0;
+    }
     if (mc) bcast_relay_kernel<true><<<ctas, kDirThreads, 0, s>>>(c->dev, pv, nvec, root, rows, fb, 0, ep, kRelayChunkVecs);
     else bcast_relay_kernel<false><<<ctas, kDirThreads, 0, s>>>(c->dev, pv, nvec, root, rows, fb, 0, ep, kRelayChunkVecs);
     DLBB_CHECK_LAUNCH("bcast_relay_kernel");

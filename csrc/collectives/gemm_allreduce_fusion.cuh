@@ -2,6 +2,8 @@
 // tile has been stored (tile_stored), the reducer warps (extra_role) and the closing barrier (finish).  Kept apart from the
 // GEMM body so that the protocol - per-tile flags, tile ownership, the addressing of the partial / output buffers, multimem
 // or peer forms - also compiles for the host emulation (emu/, tests/emu_collectives_test.cpp) with a stand-in producer.
+// Residency: a reducer waits for the partial tiles of every CTA of every rank, so the whole grid must be resident - the
+// launcher takes min(tiles, SM count) CTAs, and the GEMM's shared memory keeps it at one CTA per SM.
 #pragma once
 #include "../kernels/gemm_tiles.h"
 #if !defined(DLBB_HOST_EMU)

@@ -603,6 +603,9 @@ static void case_gemm_allreduce(World& w, int M, int N, int group_m, int grid, b
     Bufs res(w, (size_t)M * N * sizeof(T), false);
     const int num_m = (M + kBM - 1) / kBM, num_n = (N + BN - 1) / BN;
     grid = std::min(grid, std::max(2, 24 / P));   // 512 host threads per CTA and rank: stay below the process's thread limit
+    // like the launcher (grid = min(tiles, SM count), one CTA per SM): the reducers wait for tiles of every CTA, so the grid
+    // must be resident as a whole
+    if (emu::resident_ctas() > 0) grid = std::min(grid, emu::resident_ctas());
     w.run([&](int r, dlbb_comm* c) {
         T* rs = res.at<T>(r);
         const T* out = reinterpret_cast<const T*>(w.segs[out_seg].base[r]);

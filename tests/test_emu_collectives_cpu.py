@@ -78,6 +78,15 @@ def test_every_collective_at_every_world_size(emu_plain, world, mc):
     ({"DLBB_REDUCE_PULL": "1", "DLBB_REDUCE_PULL_MIN_BYTES": "8192", "DLBB_RELAY_CHUNK_KB": "1"}, 5, False, "reduce ", "reduce_pull_kernel"),
     ({"DLBB_RELAY_CHUNK_KB": "1", "EMU_CTAS": "13", "DLBB_BCAST_MC_MAX_BYTES": "0"}, 7, True, "broadcast", "bcast_relay_kernel<false>"),
     ({"DLBB_RELAY_CHUNK_KB": "1", "EMU_CTAS": "10"}, 6, False, "broadcast", "bcast_relay_kernel<false>"),
+    # push form of the relay broadcast (opt-in), on a device that holds only P-1 of its 12 CTAs at a time
+    ({"DLBB_BCAST_PUSH": "1", "DLBB_BCAST_MC_MAX_BYTES": "0", "DLBB_RELAY_CHUNK_KB": "1", "EMU_CTAS": "13", "EMU_RESIDENT_CTAS": "3"}, 4, False,
+     "broadcast", "bcast_push_kernel"),
+    ({"DLBB_BCAST_PUSH": "1", "DLBB_BCAST_MC_MAX_BYTES": "0", "DLBB_RELAY_CHUNK_KB": "1", "EMU_CTAS": "13"}, 7, True, "broadcast", "bcast_push_kernel"),
+    # two CTA slots: the two-hop pull kernels only ever wait for lower-numbered CTAs, the pipelined all-reduce is clamped
+    ({"DLBB_REDUCE_PULL": "1", "DLBB_REDUCE_PULL_MIN_BYTES": "8192", "DLBB_RELAY_CHUNK_KB": "1", "EMU_CTAS": "12", "EMU_RESIDENT_CTAS": "2",
+      "EMU_REPS": "2"}, 4, True, "reduce ", "reduce_pull_kernel"),
+    ({"DLBB_PIPELINE_MIN_BYTES": "32768", "EMU_CTAS": "4", "EMU_STAGE_KB": "256", "EMU_RESIDENT_CTAS": "2", "EMU_REPS": "2"}, 3, True,
+     "allreduce", "allreduce_pipelined_kernel"),
     ({"DLBB_DIRECT_LEGACY": "1"}, 5, False, "allreduce", "allreduce_direct_kernel"),
     ({"DLBB_MC_REDUCE_SCATTER": "1"}, 3, True, "reduce_scatter", "direct_reduce_kernel<T, OP, true, SINK_ONE"),
     ({"DLBB_MC_WORLD2": "1"}, 2, True, "allreduce", "direct_reduce_kernel<T, OP, true, SINK_MC"),
@@ -106,6 +115,7 @@ def test_threshold_selected_and_opt_in_kernels(emu_plain, env, world, mc, flt, k
     ({"EMU_REPS": "2", "DLBB_RELAY_CHUNK_KB": "1", "EMU_CTAS": "6", "DLBB_BCAST_MC_MAX_BYTES": "0"}, 4, True, "broadcast"),
     # nothing zero-copy: the staged large-message kernels (pipelined, chain, multicast broadcast) share flag bank 4
     ({"EMU_ZC_MIN": "0", "DLBB_PIPELINE_MIN_BYTES": "16384", "DLBB_CHAIN_MIN_BYTES": "16384", "EMU_CTAS": "2"}, 3, True, "mixed"),
+    ({"EMU_REPS": "3", "DLBB_BCAST_PUSH": "1", "DLBB_BCAST_MC_MAX_BYTES": "0", "DLBB_RELAY_CHUNK_KB": "1", "EMU_CTAS": "6"}, 4, True, "broadcast"),
     ({"DLBB_DEBUG_POISON": "1", "EMU_MIXED_SEEDS": "3"}, 3, False, "mixed"),   # the debug fill itself must not race with a slower reader
     ({"EMU_REPS": "2", "DLBB_PIPELINE_MIN_BYTES": "32768", "EMU_CTAS": "1", "EMU_STAGE_KB": "256"}, 2, True, "allreduce"),
 ])

@@ -38,6 +38,7 @@ WANT = {
     "reduce_pull_kernel": r"reduce_pull_kernel<__nv_bfloat16, 0, true, 8>",
     "bcast_relay_kernel_p2p": r"bcast_relay_kernel<false>",
     "bcast_relay_kernel_mc": r"bcast_relay_kernel<true>",
+    "bcast_push_kernel": r"bcast_push_kernel\(",
     "allreduce_pipelined_kernel": r"allreduce_pipelined_kernel<__nv_bfloat16, 0, true>",
     "allreduce_twoshot_kernel_nvls": r"allreduce_twoshot_kernel<__nv_bfloat16, 0, true>",
     "reduce_kernel": r"dlbb::reduce_kernel<__nv_bfloat16, 0>",
