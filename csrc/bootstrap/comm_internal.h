@@ -64,6 +64,11 @@ bool peer_registry_usable(const PeerRegistry* r);
 int peer_registry_resolve(dlbb_comm* c, PeerRegistry* r, const void* ptr, size_t bytes, PeerView* pv, bool* all_ok);
 // id of the live symmetric segment that holds [ptr, ptr + bytes) of this rank's memory, or -1
 int symm_segment_of(const dlbb_comm* c, const void* ptr, size_t bytes);
+// Flags are compared wrap-safely (signed 32-bit difference to the awaited epoch), which is only right while every flag is
+// within 2^31 of the bank's epoch counter - but a pad row that no launch has used for a long time keeps its old value.
+// Every 2^28 epochs (DLBB_FLAG_REFRESH_EVERY) the launchers therefore run a barrier over ALL rows of the bank, which
+// rewrites every flag with the current epoch.  Collective, enqueued on `stream`; returns 0 or a negative error code.
+int refresh_flag_bank_if_due(dlbb_comm* c, int bank, void* stream);
 }  // namespace dlbb
 
 struct dlbb_comm {
@@ -75,6 +80,7 @@ struct dlbb_comm {
     int pad_seg = -1, stage_seg = -1, flag_seg = -1;
     size_t stage_bytes = 0;        // bytes of each staging region: [A][B] alternate for collectives, [C] point-to-point
     uint32_t epoch[dlbb::kPadBanks] = {0, 0, 0, 0, 0, 0};  // last epoch value used on each pad bank
+    uint32_t last_refresh[dlbb::kPadBanks] = {0, 0, 0, 0, 0, 0};   // epoch at which all flags of the bank were last rewritten
     uint32_t send_epoch[DLBB_MAX_RANKS] = {};      // point-to-point: messages sent to / received from each peer
     uint32_t recv_epoch[DLBB_MAX_RANKS] = {};
     unsigned parity = 0;           // alternates the staging half used by single-barrier kernels

@@ -1543,6 +1543,25 @@ static int launch_multi(dlbb_comm* c, int dtype, int op, const MultiTable& tb, i
     return -2;
 }
 
+int refresh_flag_bank_if_due(dlbb_comm* c, int bank, void* stream) {
+    static const uint32_t every = getenv("DLBB_FLAG_REFRESH_EVERY") ? static_cast<uint32_t>(strtoul(getenv("DLBB_FLAG_REFRESH_EVERY"), nullptr, 0))
+                                                                    : (1u << 28);
+    if (c->world == 1 || c->epoch[bank] - c->last_refresh[bank] < every) return 0;
+    const uint32_t ep = ++c->epoch[bank];
+    barrier_kernel<<<kMaxCtas, 32, 0, static_cast<cudaStream_t>(stream)>>>(c->dev, bank, ep);   // row barriers: any residency
+    DLBB_CHECK_LAUNCH("barrier_kernel (flag refresh)");
+    c->last_refresh[bank] = ep;
+    return 0;
+}
+
+// the banks of this file: 0 = barriers of every kernel, 4 / 5 = chunk flags of the pipelined / chain / relay kernels
+// (bank 3, point-to-point, counts per pair of ranks and rewrites all of a pair's flags with every message)
+static int refresh_collective_flags(dlbb_comm* c, void* stream) {
+    for (int bank : {0, 4, 5})
+        if (const int rc = refresh_flag_bank_if_due(c, bank, stream)) return rc;
+    return 0;
+}
+
 }  // namespace dlbb
 
 using namespace dlbb;
@@ -1550,6 +1569,7 @@ using namespace dlbb;
 extern "C" {
 
 int dlbb_barrier(dlbb_comm_t* c, void* stream) {
+    if (const int rg = refresh_collective_flags(c, stream)) return rg;
     const uint32_t ep = ++c->epoch[0];
     barrier_kernel<<<1, 32, 0, static_cast<cudaStream_t>(stream)>>>(c->dev, 0, ep);
     DLBB_CHECK_LAUNCH("barrier_kernel");
@@ -1558,11 +1578,13 @@ int dlbb_barrier(dlbb_comm_t* c, void* stream) {
 
 int dlbb_allreduce(dlbb_comm_t* c, const void* in, void* out, int64_t count, int dtype, int op, int algo,
                    const dlbb_view_t* in_view, void* stream) {
+    if (const int rg = refresh_collective_flags(c, stream)) return rg;
     return allreduce_impl(c, in, out, nullptr, count, dtype, op, algo, in_view, static_cast<cudaStream_t>(stream));
 }
 
 int dlbb_allreduce_v(dlbb_comm_t* c, const void* in, void* out, int64_t count, int dtype, int op, int algo,
                      const dlbb_view_t* in_view, const dlbb_view_t* out_view, void* stream) {
+    if (const int rg = refresh_collective_flags(c, stream)) return rg;
     // a strided destination keeps the call on the staged kernels, whose unpack phase scatters by the view
     c->out_view = (out_view && out_view->ndim > 0) ? out_view : nullptr;
     static const dlbb_view_t kDense1 = {1, {0, 0, 0, 0}, {1, 0, 0, 0}};
@@ -1577,6 +1599,7 @@ int dlbb_allreduce_v(dlbb_comm_t* c, const void* in, void* out, int64_t count, i
 
 int dlbb_allreduce_residual_bf16(dlbb_comm_t* c, const void* in, const void* residual, void* out, int64_t count,
                                  void* stream) {
+    if (const int rg = refresh_collective_flags(c, stream)) return rg;
     return allreduce_impl(c, in, out, residual, count, DLBB_BF16, DLBB_SUM, DLBB_ALGO_AUTO, nullptr,
                           static_cast<cudaStream_t>(stream));
 }
@@ -1622,6 +1645,7 @@ static int reduce_views(dlbb_comm_t* c, const void* in, void* out, int64_t count
 
 int dlbb_reduce_v(dlbb_comm_t* c, const void* in, void* out, int64_t count, int dtype, int op, int root,
                   const dlbb_view_t* in_view, const dlbb_view_t* out_view, void* stream) {
+    if (const int rg = refresh_collective_flags(c, stream)) return rg;
     const size_t es = dtype_size(dtype);
     if ((in_view && in_view->ndim > 0) || (out_view && out_view->ndim > 0)) {
         DLBB_REQUIRE(es != 0 && dtype != DLBB_U8, "reduce: unsupported dtype %d", dtype);
@@ -1740,6 +1764,7 @@ int dlbb_reduce_v(dlbb_comm_t* c, const void* in, void* out, int64_t count, int 
 }
 
 int dlbb_reduce_scatter(dlbb_comm_t* c, const void* in, void* out, int64_t cpr, int dtype, int op, void* stream) {
+    if (const int rg = refresh_collective_flags(c, stream)) return rg;
     const size_t es = dtype_size(dtype);
     DLBB_REQUIRE(es != 0 && dtype != DLBB_U8, "reduce_scatter: unsupported dtype %d", dtype);
     if ((cpr * (int64_t)es) % 16 == 0) {   // zero-copy: rank r reduces shard r of every rank's input tensor
@@ -1788,6 +1813,7 @@ int dlbb_reduce_scatter(dlbb_comm_t* c, const void* in, void* out, int64_t cpr, 
 
 int dlbb_allgather(dlbb_comm_t* c, const void* in, void* out, int64_t cpr, int dtype, const dlbb_view_t* in_view,
                    void* stream) {
+    if (const int rg = refresh_collective_flags(c, stream)) return rg;
     const int64_t es = (int64_t)dtype_size(dtype);
     DLBB_REQUIRE(es != 0, "allgather: unsupported dtype %d", dtype);
     const int64_t total = cpr * es;
@@ -1828,6 +1854,7 @@ int dlbb_allgather(dlbb_comm_t* c, const void* in, void* out, int64_t cpr, int d
 }
 
 int dlbb_broadcast_v(dlbb_comm_t* c, void* buf, int64_t count, int dtype, int root, const dlbb_view_t* buf_view, void* stream) {
+    if (const int rg = refresh_collective_flags(c, stream)) return rg;
     const int64_t es = (int64_t)dtype_size(dtype);
     DLBB_REQUIRE(es != 0, "broadcast: unsupported dtype %d", dtype);
     DLBB_REQUIRE(root >= 0 && root < c->world, "broadcast: bad root %d", root);
@@ -1911,6 +1938,7 @@ int dlbb_gather(dlbb_comm_t* c, const void* in, void* out, int64_t count, int dt
 
 int dlbb_gather_v(dlbb_comm_t* c, const void* in, void* out, int64_t count, int dtype, int root, const dlbb_view_t* in_view,
                   void* stream) {
+    if (const int rg = refresh_collective_flags(c, stream)) return rg;
     const int64_t es = (int64_t)dtype_size(dtype);
     DLBB_REQUIRE(es != 0, "gather: unsupported dtype %d", dtype);
     DLBB_REQUIRE(root >= 0 && root < c->world, "gather: bad root %d", root);
@@ -1949,6 +1977,7 @@ int dlbb_gather_v(dlbb_comm_t* c, const void* in, void* out, int64_t count, int 
 }
 
 int dlbb_scatter(dlbb_comm_t* c, const void* in, void* out, int64_t count, int dtype, int root, void* stream) {
+    if (const int rg = refresh_collective_flags(c, stream)) return rg;
     const int64_t es = (int64_t)dtype_size(dtype);
     DLBB_REQUIRE(es != 0, "scatter: unsupported dtype %d", dtype);
     DLBB_REQUIRE(root >= 0 && root < c->world, "scatter: bad root %d", root);
@@ -1989,6 +2018,7 @@ int dlbb_scatter(dlbb_comm_t* c, const void* in, void* out, int64_t count, int d
 }
 
 int dlbb_alltoall(dlbb_comm_t* c, const void* in, void* out, int64_t cpr, int dtype, void* stream) {
+    if (const int rg = refresh_collective_flags(c, stream)) return rg;
     const int64_t es = (int64_t)dtype_size(dtype);
     DLBB_REQUIRE(es != 0, "alltoall: unsupported dtype %d", dtype);
     const int64_t total = cpr * es;
@@ -2030,6 +2060,7 @@ int dlbb_alltoall(dlbb_comm_t* c, const void* in, void* out, int64_t cpr, int dt
 
 int dlbb_sendrecv(dlbb_comm_t* c, const void* send_buf, int64_t send_count, int send_peer, void* recv_buf,
                   int64_t recv_count, int recv_peer, int dtype, void* stream) {
+    if (const int rg = refresh_collective_flags(c, stream)) return rg;
     const int64_t es = (int64_t)dtype_size(dtype);
     DLBB_REQUIRE(es != 0, "sendrecv: unsupported dtype %d", dtype);
     DLBB_REQUIRE(send_peer < c->world && recv_peer < c->world, "sendrecv: bad peer");
@@ -2058,6 +2089,7 @@ int dlbb_sendrecv(dlbb_comm_t* c, const void* send_buf, int64_t send_count, int 
 
 int dlbb_allreduce_multi(dlbb_comm_t* c, void* const* bufs, const int64_t* counts, int n_tensors, int dtype, int op,
                          void* stream) {
+    if (const int rg = refresh_collective_flags(c, stream)) return rg;
     const int64_t es = (int64_t)dtype_size(dtype);
     DLBB_REQUIRE(es != 0 && dtype != DLBB_U8, "allreduce_multi: unsupported dtype %d", dtype);
     DLBB_REQUIRE(n_tensors >= 0, "allreduce_multi: negative tensor count");
@@ -2102,11 +2134,64 @@ int dlbb_allreduce_multi(dlbb_comm_t* c, void* const* bufs, const int64_t* count
 // the message is its own tensor on both sides.  The pieces carry each tensor's offset from the first one, so the kernel
 // packs straight out of the list and pulls straight into it - no flattening copy before or after.
 int dlbb_alltoall_ptrs(dlbb_comm_t* c, const void* const* in_ptrs, void* const* out_ptrs, int64_t bytes_per_peer, void* stream) {
+    if (const int rg = refresh_collective_flags(c, stream)) return rg;
     const int64_t total = bytes_per_peer;
     const int64_t cap = static_cast<int64_t>(c->stage_bytes) / c->world / 64 * 64;
     DLBB_REQUIRE(cap > 0, "alltoall: staging too small");
     const char* in0 = static_cast<const char*>(in_ptrs[0]);
     char* out0 = static_cast<char*>(out_ptrs[0]);
+    {   // zero-copy when the input list is the chunks of one tensor (what tensor.chunk(world) gives): every rank pulls its
+        // slice out of every peer's tensor straight into the output list's tensors.  (A rank whose list is not dense, or
+        // whose outputs overlap its input, enters the exchange with a null buffer and all ranks stage together.)
+        bool dense = total > 0;
+        for (int p = 0; p < c->world && dense; ++p) {
+            dense = static_cast<const char*>(in_ptrs[p]) == in0 + p * total;
+            dense = dense && disjoint(in0, total * c->world, out_ptrs[p], total);
+        }
+        PeerView pv;
+        bool zc = false;
+        const int rc = try_zero_copy(c, dense ? in0 : nullptr, total * c->world, total * c->world, &pv, &zc, in0);
+        if (rc) return rc;
+        if (zc) {
+            PieceList pull{};
+            pull.count = c->world;
+            for (int i = 0; i < c->world; ++i) {
+                const int p = (c->rank + i) % c->world;
+                pull.p[i] = Piece{p, c->rank * total, static_cast<char*>(out_ptrs[p]) - out0, total};
+            }
+            return launch_move(c, in0, out0, PieceList{}, pull, ViewDev{}, 1, total * c->world, static_cast<cudaStream_t>(stream), &pv);
+        }
+        // Separate tensors (the reference's loop clones every chunk): one exchange per list position - exchange j tells
+        // rank j where every peer keeps the tensor meant for it.  All ranks take part in all of them and see every
+        // outcome, so they agree on falling back.  Worth `world` host round trips (~0.2 ms on 8 ranks) only for large
+        // messages: the gate is the size of ONE tensor (DLBB_A2A_LIST_ZC_MIN_BYTES, default 64 MiB - at 16 MiB per peer
+        // the staged form measured 1.27x NCCL on 8 GPUs and stays; at 128 MiB per peer it measured 0.74x).
+        static const int64_t list_zc_min = getenv("DLBB_A2A_LIST_ZC_MIN_BYTES") ? atoll(getenv("DLBB_A2A_LIST_ZC_MIN_BYTES")) : (64ll << 20);
+        if (!dense && c->zero_copy_min > 0 && total >= list_zc_min && total >= (int64_t)c->zero_copy_min) {
+            PeerView mine{};
+            bool all = true;
+            for (int j = 0; j < c->world; ++j) {
+                bool ok_j = false;
+                bool usable = true;
+                for (int p = 0; p < c->world; ++p) usable = usable && disjoint(in_ptrs[j], total, out_ptrs[p], total);
+                PeerView pj;
+                const int rc2 = try_zero_copy(c, usable ? in_ptrs[j] : nullptr, total, total, &pj, &ok_j, in_ptrs[j]);
+                if (rc2) return rc2;
+                all = all && ok_j;
+                if (j == c->rank) mine = pj;
+            }
+            if (all) {
+                PieceList pull{};
+                pull.count = c->world;
+                for (int i = 0; i < c->world; ++i) {
+                    const int p = (c->rank + i) % c->world;
+                    pull.p[i] = Piece{p, 0, static_cast<char*>(out_ptrs[p]) - out0, total};
+                }
+                mine.mc = nullptr;
+                return launch_move(c, in0, out0, PieceList{}, pull, ViewDev{}, 1, total * c->world, static_cast<cudaStream_t>(stream), &mine);
+            }
+        }
+    }
     for (int64_t done = 0; done < total || (total == 0 && done == 0); done += cap) {
         const int64_t n = std::min(cap, total - done);
         if (n <= 0) break;
@@ -2130,6 +2215,7 @@ int dlbb_alltoall_ptrs(dlbb_comm_t* c, const void* const* in_ptrs, void* const* 
 // contribution is pulled straight into out_ptrs[p].  root < 0: all-gather; otherwise only the root receives.
 int dlbb_allgather_ptrs(dlbb_comm_t* c, const void* in, void* const* out_ptrs, int64_t count, int dtype, int root,
                         const dlbb_view_t* in_view, void* stream) {
+    if (const int rg = refresh_collective_flags(c, stream)) return rg;
     const int64_t es = (int64_t)dtype_size(dtype);
     DLBB_REQUIRE(es != 0, "allgather: unsupported dtype %d", dtype);
     DLBB_REQUIRE(root < c->world, "gather: bad root %d", root);

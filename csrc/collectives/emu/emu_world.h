@@ -77,6 +77,8 @@ struct World {
                     for (int p = 0; p < P; ++p) {
                         uint32_t* w = reinterpret_cast<uint32_t*>(pads.base[p]);
                         for (size_t i = 0; i < dlbb::kPadBytes / 4; ++i) w[i] = v;
+                        uint32_t* tf = reinterpret_cast<uint32_t*>(flags.base[p]);   // per-tile flags of the fused GEMM + all-reduce
+                        for (size_t i = 0; i < dlbb::kTileFlagBytes / 4; ++i) tf[i] = v;
                     }
             }
             const char* wd = getenv("DLBB_WATCHDOG_SECONDS");

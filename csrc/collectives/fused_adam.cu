@@ -174,6 +174,7 @@ extern "C" int dlbb_fused_reduce_adam_bf16(dlbb_comm_t* c, int grads_seg, int pa
         ctas = static_cast<int>(std::max<int64_t>(1, std::min<int64_t>(c->ctas > 0 ? c->ctas : 120, want_all)));
         ctas = std::min(ctas, kMaxCtas);
     }
+    if (const int rg = refresh_flag_bank_if_due(c, kFusedBank, stream)) return rg;   // (comm_internal.h: flags stay within 2^31 of the epoch)
     const uint32_t ep = c->epoch[kFusedBank] + 1;
     c->epoch[kFusedBank] += 2;
     cudaStream_t s = static_cast<cudaStream_t>(stream);

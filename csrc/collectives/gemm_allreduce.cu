@@ -96,6 +96,20 @@ extern "C" int dlbb_gemm_allreduce_bf16(dlbb_comm_t* c, const void* A, const voi
     f.residual = static_cast<const __nv_bfloat16*>(residual);
     f.ld_res = ld_res;
     f.M = M; f.N = N; f.bn = BN; f.num_m = num_m; f.num_n = num_n; f.num_tiles = num_m * num_n; f.group_m = p.group_m;
+    {
+        static const uint32_t every = getenv("DLBB_FLAG_REFRESH_EVERY") ? static_cast<uint32_t>(strtoul(getenv("DLBB_FLAG_REFRESH_EVERY"), nullptr, 0))
+                                                                        : (1u << 28);
+        if (c->world > 1 && c->epoch[kArBank] - c->last_refresh[kArBank] >= every) {
+            // rows of the bank first (a barrier over all of them), then the tile flags
+            c->last_refresh[kArBank] = c->epoch[kArBank] - every;   // make the bank refresh due now, whatever its own history
+            if (const int rg = refresh_flag_bank_if_due(c, kArBank, stream)) return rg;
+            const uint32_t ep = c->epoch[kArBank] + 1;
+            c->epoch[kArBank] += 2;
+            refresh_tile_flags_kernel<<<64, 256, 0, static_cast<cudaStream_t>(stream)>>>(c->dev, ep);
+            DLBB_CHECK_LAUNCH("refresh_tile_flags_kernel");
+            c->last_refresh[kArBank] = c->epoch[kArBank];
+        }
+    }
     f.epoch = ++c->epoch[kArBank];
     // every rank must launch the same grid: CTA b meets CTA b of the peers at the end
     const int grid = std::min(std::min(num_m * num_n, sms), kMaxCtas);

@@ -142,4 +142,15 @@ struct ArFusion {
     __device__ __forceinline__ void finish() { row_barrier(c, kArBank, blockIdx.x, epoch); }
 };
 
+// Per-tile flags that no call has used for a long time (a larger GEMM after many smaller ones) must stay within 2^31 of
+// the epoch counter (comm_internal.h: refresh_flag_bank_if_due): between two row barriers every rank rewrites its own
+// flag array with the current epoch.
+__global__ void refresh_tile_flags_kernel(CommDev c, uint32_t epoch) {
+    row_barrier(c, kArBank, blockIdx.x, epoch);
+    const size_t n = kMaxFusedTiles * (size_t)c.world;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+        st_release_sys(c.tile_flags[c.rank] + i, epoch + 1);
+    row_barrier(c, kArBank, blockIdx.x, epoch + 1);
+}
+
 }  // namespace dlbb

@@ -348,7 +348,7 @@ static void case_ptrs(World& w, int64_t n, int root) {
     char name[160];
     snprintf(name, sizeof(name), "allgather_ptrs/alltoall_ptrs %s n=%lld root=%d", DT<T>::name, (long long)n, root);
     g_case = name;
-    Bufs in(w, n * sizeof(T), false);
+    Bufs in(w, n * sizeof(T), false), dense_in(w, n * w.P * sizeof(T), false);
     std::vector<Bufs> outs, a2a_in, a2a_out;
     for (int p = 0; p < w.P; ++p) {
         outs.emplace_back(w, n * sizeof(T), false);
@@ -374,7 +374,17 @@ static void case_ptrs(World& w, int64_t n, int root) {
             CALL(dlbb_alltoall_ptrs(c, ai.data(), ao.data(), n * (int64_t)sizeof(T), nullptr));
             for (int p = 0; p < w.P; ++p)
                 if (!expect_eq(static_cast<T*>(ao[p]), n, p, rep, 1000 * r, r, "alltoall_ptrs")) break;
-            g_checks.fetch_add(2);
+            // the same with the input list being the chunks of ONE tensor (tensor.chunk(world)): zero-copy from 8 KiB
+            T* flat = dense_in.at<T>(r);
+            for (int p = 0; p < w.P; ++p) {
+                mfill(flat + p * n, r, n, rep, 2000 * p);
+                ai[p] = flat + p * n;
+                memset(ao[p], 0x22, n * sizeof(T));
+            }
+            CALL(dlbb_alltoall_ptrs(c, ai.data(), ao.data(), n * (int64_t)sizeof(T), nullptr));
+            for (int p = 0; p < w.P; ++p)
+                if (!expect_eq(static_cast<T*>(ao[p]), n, p, rep, 2000 * r, r, "alltoall_ptrs (dense list)")) break;
+            g_checks.fetch_add(3);
         }
     });
 }
@@ -612,6 +622,13 @@ static void case_gemm_allreduce(World& w, int M, int N, int group_m, int grid, b
         for (int rep = 0; rep < kReps; ++rep) {
             if (with_residual)
                 for (int64_t e = 0; e < (int64_t)M * N; ++e) rs[e] = from_d<T>(static_cast<double>((e + rep) % 3));
+            if (rep % 2 == 1) {   // the launcher's periodic flag refresh (every 2^28 calls there, every other call here)
+                c->last_refresh[kArBank] = c->epoch[kArBank] - (1u << 28);
+                CALL(refresh_flag_bank_if_due(c, kArBank, nullptr));
+                const uint32_t ep = c->epoch[kArBank] + 1;
+                c->epoch[kArBank] += 2;
+                EMU_LAUNCH(4, 256, refresh_tile_flags_kernel)(c->dev, ep);
+            }
             ArFusion f{};   // as dlbb_gemm_allreduce_bf16 fills it
             f.c = c->dev;
             for (int q = 0; q < P; ++q) {

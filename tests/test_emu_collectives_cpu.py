@@ -59,7 +59,7 @@ def _ran(kernels, prefix):
 @pytest.mark.parametrize("world,mc", [(2, True), (3, True), (5, False), (6, True), (7, False), (8, True)])   # (4: below, twice)
 def test_every_collective_at_every_world_size(emu_plain, world, mc):
     out, k = _run(emu_plain, world, mc, env={"EMU_REPS": "2", "EMU_MIXED_SEEDS": "2"})
-    assert _ran(k, "fused_reduce_adam_kernel") and _ran(k, "emu_gemm_allreduce_kernel"), k
+    assert _ran(k, "fused_reduce_adam_kernel") and _ran(k, "emu_gemm_allreduce_kernel") and _ran(k, "refresh_tile_flags_kernel"), k
     assert _ran(k, "reduce_kernel") and _ran(k, "move_kernel") and _ran(k, "p2p_kernel") and _ran(k, "reduce_multi_kernel"), k
     assert _ran(k, "direct_reduce_kernel"), k                      # zero-copy in place
     if world > 2:
@@ -87,6 +87,7 @@ def test_every_collective_at_every_world_size(emu_plain, world, mc):
       "EMU_REPS": "2"}, 4, True, "reduce ", "reduce_pull_kernel"),
     ({"DLBB_PIPELINE_MIN_BYTES": "32768", "EMU_CTAS": "4", "EMU_STAGE_KB": "256", "EMU_RESIDENT_CTAS": "2", "EMU_REPS": "2"}, 3, True,
      "allreduce", "allreduce_pipelined_kernel"),
+    ({"DLBB_A2A_LIST_ZC_MIN_BYTES": "4096"}, 5, False, "ptrs", "move_kernel"),    # list all-to-all on separate tensors, zero-copy
     ({"DLBB_DIRECT_LEGACY": "1"}, 5, False, "allreduce", "allreduce_direct_kernel"),
     ({"DLBB_MC_REDUCE_SCATTER": "1"}, 3, True, "reduce_scatter", "direct_reduce_kernel<T, OP, true, SINK_ONE"),
     ({"DLBB_MC_WORLD2": "1"}, 2, True, "allreduce", "direct_reduce_kernel<T, OP, true, SINK_MC"),
@@ -95,6 +96,8 @@ def test_every_collective_at_every_world_size(emu_plain, world, mc):
     ({"DLBB_DEBUG_POISON": "1", "EMU_REPS": "2"}, 4, True, None, "reduce_kernel"),                          # 0xFF-filled staging
     # a device with 3 CTA slots and 7 CTAs asked for: grid-barrier kernels are clamped, the others run in waves
     ({"EMU_CTAS": "7", "EMU_RESIDENT_CTAS": "3", "EMU_REPS": "2", "EMU_MIXED_SEEDS": "2"}, 4, True, None, "move_kernel"),
+    # the periodic rewrite of all flags of a bank (every 2^28 epochs in production, every 40 here), across the wrap
+    ({"DLBB_FLAG_REFRESH_EVERY": "40", "EMU_EPOCH0": "0xFFFFFF00", "EMU_REPS": "2", "EMU_MIXED_SEEDS": "2"}, 3, True, None, "barrier_kernel"),
     ({"EMU_EPOCH0": "0xFFFFFFC0", "EMU_REPS": "3"}, 3, True, None, "reduce_kernel"),                       # every epoch counter wraps past 2^32
 ])
 def test_threshold_selected_and_opt_in_kernels(emu_plain, env, world, mc, flt, kernel):
