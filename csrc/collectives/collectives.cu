@@ -2060,7 +2060,7 @@ int dlbb_alltoall(dlbb_comm_t* c, const void* in, void* out, int64_t cpr, int dt
 
 int dlbb_sendrecv(dlbb_comm_t* c, const void* send_buf, int64_t send_count, int send_peer, void* recv_buf,
                   int64_t recv_count, int recv_peer, int dtype, void* stream) {
-    if (const int rg = refresh_collective_flags(c, stream)) return rg;
+    // (no flag refresh here: point-to-point calls may run on their own stream beside a collective, and bank 3 needs none)
     const int64_t es = (int64_t)dtype_size(dtype);
     DLBB_REQUIRE(es != 0, "sendrecv: unsupported dtype %d", dtype);
     DLBB_REQUIRE(send_peer < c->world && recv_peer < c->world, "sendrecv: bad peer");

