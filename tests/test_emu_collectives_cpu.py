@@ -56,11 +56,14 @@ def _ran(kernels, prefix):
     return sum(n for k, n in kernels.items() if k.startswith(prefix))
 
 
-@pytest.mark.parametrize("world,mc", [(2, True), (3, True), (5, False), (7, False), (8, True)])   # (4 and 6: below)
+@pytest.mark.parametrize("world,mc", [(1, False), (2, True), (3, True), (5, False), (7, False), (8, True)])   # (4 and 6: below)
 def test_every_collective_at_every_world_size(emu_plain, world, mc):
     out, k = _run(emu_plain, world, mc, env={"EMU_REPS": "2", "EMU_MIXED_SEEDS": "2"})
-    assert _ran(k, "fused_reduce_adam_kernel") and _ran(k, "emu_gemm_allreduce_kernel") and _ran(k, "refresh_tile_flags_kernel"), k
-    assert _ran(k, "reduce_kernel") and _ran(k, "move_kernel") and _ran(k, "p2p_kernel") and _ran(k, "reduce_multi_kernel"), k
+    assert _ran(k, "fused_reduce_adam_kernel") and _ran(k, "emu_gemm_allreduce_kernel"), k
+    assert _ran(k, "reduce_kernel") and _ran(k, "move_kernel"), k
+    if world == 1:   # what the driver's one-GPU box runs: every collective degenerates to a local copy / reduction
+        return
+    assert _ran(k, "refresh_tile_flags_kernel") and _ran(k, "p2p_kernel") and _ran(k, "reduce_multi_kernel"), k
     assert _ran(k, "direct_reduce_kernel"), k                      # zero-copy in place
     if world > 2:
         assert _ran(k, "bcast_relay_kernel"), k
