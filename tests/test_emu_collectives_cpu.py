@@ -97,6 +97,8 @@ def test_every_collective_at_every_world_size(emu_plain, world, mc):
     ({"DLBB_FUSION": "0"}, 3, True, "multi", "reduce_kernel"),
     ({"EMU_CTAS": "1", "EMU_STAGE_KB": "16", "EMU_ZC_MIN": "0", "EMU_REPS": "2"}, 4, True, None, "allreduce_twoshot_kernel"),   # everything staged, many slices
     ({"DLBB_DEBUG_POISON": "1", "EMU_REPS": "2"}, 4, True, None, "reduce_kernel"),                          # 0xFF-filled staging
+    # DLBB_CTAS unset: the launchers' own grid choices (up to 294 CTAs for the two-hop kernels)
+    ({"EMU_CTAS": "0", "EMU_REPS": "2", "EMU_MIXED_SEEDS": "2"}, 3, True, None, "bcast_relay_kernel"),
     # a device with 3 CTA slots and 7 CTAs asked for: grid-barrier kernels are clamped, the others run in waves
     ({"EMU_CTAS": "7", "EMU_RESIDENT_CTAS": "3", "EMU_REPS": "2", "EMU_MIXED_SEEDS": "2"}, 4, True, None, "move_kernel"),
     # the periodic rewrite of all flags of a bank (every 2^28 epochs in production, every 40 here), across the wrap
