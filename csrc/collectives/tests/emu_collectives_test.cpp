@@ -788,7 +788,7 @@ int main(int argc, char** argv) {
         printf("watchdog did not fire\n");
         return 3;
     }
-    const int64_t sizes[] = {1, 7, 300, 4099, 20000, 70001};
+    const int64_t sizes[] = {0, 1, 7, 300, 4099, 20000, 70001};
     if (want(filter, "allreduce")) {
         for (int64_t n : sizes) {
             for (int algo : {DLBB_ALGO_AUTO, DLBB_ALGO_ONESHOT, DLBB_ALGO_TWOSHOT, DLBB_ALGO_NVLS}) {
