@@ -116,6 +116,8 @@ def test_threshold_selected_and_opt_in_kernels(emu_plain, env, world, mc, flt, k
     ({}, 4, False, "mixed"),
     ({"EMU_REPS": "3"}, 3, True, "views"),
     ({"EMU_REPS": "3"}, 3, False, "sendrecv"),
+    ({"EMU_REPS": "3", "DLBB_A2A_LIST_ZC_MIN_BYTES": "4096"}, 3, False, "ptrs"),   # list collectives, zero-copy on separate tensors
+    ({"EMU_REPS": "3"}, 4, True, "multi"),                                         # bucket fusion
     ({"EMU_REPS": "3"}, 3, True, "fused_adam"),
     ({"EMU_REPS": "3"}, 3, True, "gemm_allreduce"),     # reducer warps + per-tile flags of the fused GEMM + all-reduce
     ({"EMU_REPS": "3"}, 4, False, "gemm_allreduce"),
