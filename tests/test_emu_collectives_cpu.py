@@ -26,18 +26,37 @@ def _build(tmp_path_factory, name, *extra):
     return out
 
 
-@pytest.fixture(scope="module")
-def emu_plain(tmp_path_factory):
-    return _build(tmp_path_factory, "emu_collectives")
-
-
-@pytest.fixture(scope="module")
-def emu_tsan(tmp_path_factory):
-    probe = subprocess.run(["g++", "-fsanitize=thread", "-x", "c++", "-", "-o", "/dev/null"], input="int main(){}", text=True,
+def _sanitizer_available(kind):
+    probe = subprocess.run(["g++", f"-fsanitize={kind}", "-x", "c++", "-", "-o", "/dev/null"], input="int main(){}", text=True,
                            capture_output=True)
-    if probe.returncode != 0:
+    return probe.returncode == 0
+
+
+@pytest.fixture(scope="module")
+def emu_builds(tmp_path_factory):
+    """All variants of the emulation build, compiled side by side (one g++ each, about a minute)."""
+    from concurrent.futures import ThreadPoolExecutor
+    variants = {"plain": ()}
+    if _sanitizer_available("thread"):
+        variants["tsan"] = ("--sanitize", "thread")
+        variants["weak"] = ("--sanitize", "thread", "--define", "EMU_WEAK_FLAGS")
+    if _sanitizer_available("address"):
+        variants["asan"] = ("--sanitize", "address")
+    with ThreadPoolExecutor(max_workers=len(variants)) as pool:
+        futs = {k: pool.submit(_build, tmp_path_factory, "emu_collectives_" + k, *extra) for k, extra in variants.items()}
+        return {k: f.result() for k, f in futs.items()}
+
+
+@pytest.fixture(scope="module")
+def emu_plain(emu_builds):
+    return emu_builds["plain"]
+
+
+@pytest.fixture(scope="module")
+def emu_tsan(emu_builds):
+    if "tsan" not in emu_builds:
         pytest.skip("ThreadSanitizer runtime not available")
-    return _build(tmp_path_factory, "emu_collectives_tsan", "--sanitize", "thread")
+    return emu_builds["tsan"]
 
 
 def _run(exe, world, mc, flt=None, env=None, timeout=1500):
@@ -150,21 +169,19 @@ def test_grid_barrier_over_more_ctas_than_fit_is_detected(emu_plain):
     assert r.returncode != 0 and "device barrier timeout" in r.stderr, r.stderr[-2000:]
 
 
-def test_no_out_of_bounds_access_under_address_sanitizer(tmp_path_factory):
+def test_no_out_of_bounds_access_under_address_sanitizer(emu_builds):
     """Tensors are allocated to the byte: a kernel that rounds a tail up to a whole vector, or view arithmetic that leaves the
     tensor, is an AddressSanitizer report."""
-    probe = subprocess.run(["g++", "-fsanitize=address", "-x", "c++", "-", "-o", "/dev/null"], input="int main(){}", text=True,
-                           capture_output=True)
-    if probe.returncode != 0:
+    if "asan" not in emu_builds:
         pytest.skip("AddressSanitizer runtime not available")
-    exe = _build(tmp_path_factory, "emu_collectives_asan", "--sanitize", "address")
-    out, _ = _run(exe, 3, True, env={"EMU_REPS": "1", "EMU_MIXED_SEEDS": "1", "ASAN_OPTIONS": "detect_leaks=0"})
+    out, _ = _run(emu_builds["asan"], 3, True, env={"EMU_REPS": "1", "EMU_MIXED_SEEDS": "1", "ASAN_OPTIONS": "detect_leaks=0"})
     assert "AddressSanitizer" not in out, out[-4000:]
 
 
-def test_thread_sanitizer_sees_the_protocol(tmp_path_factory, emu_tsan):
+def test_thread_sanitizer_sees_the_protocol(emu_builds):
     """Negative control: with the flags demoted to relaxed atomics the same run must report data races."""
-    weak = _build(tmp_path_factory, "emu_collectives_weak", "--sanitize", "thread", "--define", "EMU_WEAK_FLAGS")
-    r = subprocess.run([str(weak), "2", "mc", "allreduce"], capture_output=True, text=True, timeout=1500,
+    if "weak" not in emu_builds:
+        pytest.skip("ThreadSanitizer runtime not available")
+    r = subprocess.run([str(emu_builds["weak"]), "2", "mc", "allreduce"], capture_output=True, text=True, timeout=1500,
                        env=dict(os.environ, EMU_REPS="2"))
     assert "WARNING: ThreadSanitizer: data race" in r.stderr
