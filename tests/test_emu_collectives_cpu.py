@@ -61,6 +61,7 @@ def emu_tsan(emu_builds):
 
 def _run(exe, world, mc, flt=None, env=None, timeout=1500):
     e = dict(os.environ)
+    e.setdefault("EMU_REPS", "2")   # back-to-back repetitions per case (the program's own default is 4)
     e.update(env or {})
     cmd = [str(exe), str(world), "mc" if mc else "nomc"] + ([flt] if flt else [])
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=timeout, env=e)
@@ -117,11 +118,12 @@ def test_every_collective_at_every_world_size(emu_plain, world, mc):
     ({"EMU_CTAS": "1", "EMU_STAGE_KB": "16", "EMU_ZC_MIN": "0", "EMU_REPS": "2"}, 4, True, None, "allreduce_twoshot_kernel"),   # everything staged, many slices
     ({"DLBB_DEBUG_POISON": "1", "EMU_REPS": "2"}, 4, True, None, "reduce_kernel"),                          # 0xFF-filled staging
     # DLBB_CTAS unset: the launchers' own grid choices (up to 294 CTAs for the two-hop kernels)
-    ({"EMU_CTAS": "0", "EMU_REPS": "2", "EMU_MIXED_SEEDS": "2"}, 3, True, None, "bcast_relay_kernel"),
+    ({"EMU_CTAS": "0"}, 3, True, "broadcast", "bcast_relay_kernel"),
+    ({"EMU_CTAS": "0"}, 3, True, "allreduce", "direct_reduce_kernel"),
     # a device with 3 CTA slots and 7 CTAs asked for: grid-barrier kernels are clamped, the others run in waves
     ({"EMU_CTAS": "7", "EMU_RESIDENT_CTAS": "3", "EMU_REPS": "2", "EMU_MIXED_SEEDS": "2"}, 4, True, None, "move_kernel"),
-    # the periodic rewrite of all flags of a bank (every 2^28 epochs in production, every 40 here), across the wrap
-    ({"DLBB_FLAG_REFRESH_EVERY": "40", "EMU_EPOCH0": "0xFFFFFF00", "EMU_REPS": "2", "EMU_MIXED_SEEDS": "2"}, 3, True, None, "barrier_kernel"),
+    # the periodic rewrite of all flags of a bank (every 2^28 epochs in production, every 300 here), across the wrap
+    ({"DLBB_FLAG_REFRESH_EVERY": "300", "EMU_EPOCH0": "0xFFFFFF00", "EMU_REPS": "2", "EMU_MIXED_SEEDS": "2"}, 3, True, None, "barrier_kernel"),
     ({"EMU_EPOCH0": "0xFFFFFFC0", "EMU_REPS": "3"}, 3, True, None, "reduce_kernel"),                       # every epoch counter wraps past 2^32
 ])
 def test_threshold_selected_and_opt_in_kernels(emu_plain, env, world, mc, flt, kernel):
@@ -138,8 +140,7 @@ def test_threshold_selected_and_opt_in_kernels(emu_plain, env, world, mc, flt, k
     ({"EMU_REPS": "3", "DLBB_A2A_LIST_ZC_MIN_BYTES": "4096"}, 3, False, "ptrs"),   # list collectives, zero-copy on separate tensors
     ({"EMU_REPS": "3"}, 4, True, "multi"),                                         # bucket fusion
     ({"EMU_REPS": "3"}, 3, True, "fused_adam"),
-    ({"EMU_REPS": "3"}, 3, True, "gemm_allreduce"),     # reducer warps + per-tile flags of the fused GEMM + all-reduce
-    ({"EMU_REPS": "3"}, 4, False, "gemm_allreduce"),
+    ({"EMU_REPS": "2"}, 3, True, "gemm_allreduce"),     # reducer warps + per-tile flags of the fused GEMM + all-reduce
     ({"EMU_REPS": "2", "DLBB_REDUCE_PULL": "1", "DLBB_REDUCE_PULL_MIN_BYTES": "8192", "DLBB_RELAY_CHUNK_KB": "1"}, 4, True, "reduce "),
     ({"EMU_REPS": "2", "DLBB_RELAY_CHUNK_KB": "1", "EMU_CTAS": "6", "DLBB_BCAST_MC_MAX_BYTES": "0"}, 4, True, "broadcast"),
     # nothing zero-copy: the staged large-message kernels (pipelined, chain, multicast broadcast) share flag bank 4
